@@ -1,0 +1,62 @@
+"""Contiguous block partition of a cost sequence (Barany & Grinberg,
+"Block Partitions of Sequences", arXiv:1308.2452).
+
+Start from equal-length blocks and repeatedly slide one boundary element from
+the neighbour towards the currently lightest block, walking from the heaviest
+block's side, until the heaviest and lightest block differ by at most one
+(costs normalised to [0, 1]). Not optimal, but O(k n^3) and good enough for
+stage balancing. Contract: reference ``torchgpipe/balance/blockpartition.py:11-89``
+(e.g. ``solve([1,2,3,4,5,6], 2) == [[1,2,3,4],[5,6]]``).
+"""
+from typing import List
+
+__all__ = ['solve']
+
+
+def solve(sequence: List[int], partitions: int = 1) -> List[List[int]]:
+    """Splits ``sequence`` into ``partitions`` contiguous blocks of similar sum."""
+    if partitions < 1:
+        raise ValueError(f'partitions must be a positive integer ({partitions} < 1)')
+
+    n = len(sequence)
+    if n < partitions:
+        raise ValueError(f'sequence is shorter than intended partitions ({n} < {partitions})')
+
+    lo = min(sequence)
+    spread = max(sequence) - lo
+    if spread == 0:
+        weights = [0.0] * n
+    else:
+        weights = [(x - lo) / spread for x in sequence]
+
+    # ends[b] is the exclusive end index of block b.
+    ends = [n // partitions * (b + 1) for b in range(partitions - 1)] + [n]
+
+    def weight_of(b: int) -> float:
+        begin = ends[b - 1] if b > 0 else 0
+        return sum(weights[begin:ends[b]])
+
+    def blocks() -> List[List[int]]:
+        begins = [0] + ends[:-1]
+        return [sequence[a:z] for a, z in zip(begins, ends)]
+
+    while True:
+        # Heaviest block (ties -> highest index), as in the paper's step (1).
+        heavy_weight, heavy = max((weight_of(b), b) for b in range(partitions))
+
+        while True:
+            light_weight, light = min((weight_of(b), b) for b in range(partitions))
+            if heavy_weight <= light_weight + 1:
+                return blocks()
+
+            if heavy < light:
+                # Give the last element of the block left of `light` to `light`.
+                neighbour = light - 1
+                ends[neighbour] -= 1
+            else:
+                # Give the first element of the block right of `light` to `light`.
+                neighbour = light + 1
+                ends[light] += 1
+
+            if neighbour == heavy:
+                break   # the heaviest block changed: re-evaluate from step (1)

@@ -1,0 +1,475 @@
+"""``DistributedGPipe``: one process per pipeline stage.
+
+Each rank builds the full ``nn.Sequential``, keeps only its own stage
+(:func:`get_module_partition`) and exchanges micro-batches with its
+neighbours through a :class:`~torchgpipe_b200.distributed.transport.Transport`.
+
+Public surface follows reference ``torchgpipe/distributed/gpipe.py:26-275``:
+``DistributedGPipe(module, rank, workers, balance, microbatch_chunks, *, device,
+deferred_batch_norm)`` with ``forward(batch_or_None) -> list of per-micro-batch
+outputs``, ``backward(losses_or_None)``, ``model()``; static hooks
+``_get/_put`` remain the patch points of the queue backend. Added on top
+(absent in the reference): ``checkpoint=`` modes, cross-stage
+``@skippable`` routes (sent directly from the stashing rank to the popping
+rank), a working ``deferred_batch_norm``, and device-resident NCCL transfers.
+
+Per micro-batch the stage is one function ``(boundary inputs + popped skips)
+-> (outputs + stashed skips)``; with checkpointing that function is wrapped by
+the same ``Checkpoint``/``Recompute`` pair as in single-process mode, so
+``backward`` is a single ``torch.autograd.backward`` whose roots are the
+stage outputs and the stashed skips.
+"""
+from collections import OrderedDict
+from typing import Any, Dict, Iterable, Iterator, List, Optional, Tuple, Union
+
+import torch
+from torch import Tensor, nn
+
+from torchgpipe_b200 import microbatch
+from torchgpipe_b200.batchnorm import DeferredBatchNorm
+from torchgpipe_b200.checkpoint import Checkpointing, is_recomputing
+from torchgpipe_b200.distributed import context
+from torchgpipe_b200.distributed.transport import ChannelTransport, Transport
+from torchgpipe_b200.distributed.utils import to
+from torchgpipe_b200.gpipe import (BalanceError, check_balance, recommend_auto_balance,
+                                   verify_module)
+from torchgpipe_b200.microbatch import Batch
+from torchgpipe_b200.skip.layout import inspect_skip_layout
+from torchgpipe_b200.skip.namespace import Namespace
+from torchgpipe_b200.skip.skippable import Skippable, verify_skippables
+from torchgpipe_b200.skip.tracker import SkipTracker, use_skip_tracker
+
+__all__ = ['DistributedGPipe', 'DistributedGPipeDataLoader', 'get_module_partition']
+
+Tensors = Tuple[Tensor, ...]
+TensorOrTensors = Union[Tensor, Tensors]
+SkipKey = Tuple[Namespace, str]
+
+
+def _stage_slices(module: nn.Sequential, balance: List[int]) -> List['OrderedDict[str, nn.Module]']:
+    named = iter(module.named_children())
+    return [OrderedDict(next(named) for _ in range(count)) for count in balance]
+
+
+def get_module_partition(module: nn.Sequential,
+                         rank: int,
+                         balance: Iterable[int],
+                         device: Optional[torch.device],
+                         ) -> nn.Sequential:
+    """Returns stage ``rank`` of ``module`` under ``balance`` (children keep their names),
+    moved to ``device`` unless that is ``None``."""
+    balance = list(balance)
+    check_balance(module, balance)
+    if not 0 <= rank < len(balance):
+        raise RuntimeError('module and balance mismatch')
+    partition = nn.Sequential(_stage_slices(module, balance)[rank])
+    if device is not None:
+        partition.to(device)
+    return partition
+
+
+class _StageSkipTracker(SkipTracker):
+    """Tracker of one micro-batch on one rank: cross-stage skips use in/out boxes."""
+
+    def __init__(self, incoming: Dict[SkipKey, Optional[Tensor]], outgoing_keys: List[SkipKey]):
+        super().__init__()
+        self.incoming = incoming
+        self.outgoing_keys = set(outgoing_keys)
+        self.outgoing: Dict[SkipKey, Optional[Tensor]] = {}
+
+    def save(self, batch: Batch, ns: Namespace, name: str, tensor: Optional[Tensor]) -> None:
+        if (ns, name) in self.outgoing_keys:
+            self.outgoing[(ns, name)] = tensor
+        else:
+            super().save(batch, ns, name, tensor)
+
+    def load(self, batch: Batch, ns: Namespace, name: str) -> Optional[Tensor]:
+        if (ns, name) in self.incoming:
+            return self.incoming.pop((ns, name))
+        return super().load(batch, ns, name)
+
+
+class _Flight:
+    """Everything a rank keeps about one micro-batch between forward and backward."""
+
+    __slots__ = ('leaves', 'n_boundary', 'outputs', 'n_outputs', 'atomic', 'atomic_in')
+
+    def __init__(self) -> None:
+        self.leaves: Tensors = ()
+        self.n_boundary = 0
+        self.outputs: Tensors = ()
+        self.n_outputs = 0
+        self.atomic = True
+        self.atomic_in = True
+
+
+class DistributedGPipe:
+    """Stage-per-process GPipe. Not an ``nn.Module``; see :meth:`model`.
+
+    Args:
+        module: the *whole* sequential model (every rank builds the same one).
+        rank: this process's stage index.
+        workers: ``{stage rank: unique worker name}``.
+        balance: layers per stage.
+        microbatch_chunks: number of micro-batches.
+
+    Keyword Args:
+        device: device of this stage (``None`` = leave the module where it is).
+        deferred_batch_norm: convert BatchNorm layers of this stage.
+        checkpoint: ``'never'`` (default, reference behaviour), ``'except_last'``
+            or ``'always'``.
+        transport: a :class:`Transport`; default is the in-process channel
+            backend driven through ``_put``/``_get``.
+    """
+
+    #: The number of micro-batches.
+    chunks: int = 1
+
+    # Patch points of the channel backend (reference gpipe.py:83-96).
+    @staticmethod
+    def _get(name: str, id: int, backward: bool = False) -> TensorOrTensors:
+        func = context.get_backward if backward else context.get_forward
+        return func(name, id)
+
+    @staticmethod
+    def _put(name: str, id: int, values: TensorOrTensors, backward: bool = False) -> None:
+        func = context.put_backward if backward else context.put_forward
+        func(name, id, values)
+
+    def __init__(self,
+                 module: nn.Sequential,
+                 rank: int,
+                 workers: Dict[int, str],
+                 balance: Optional[Iterable[int]] = None,
+                 microbatch_chunks: int = chunks,
+                 *,
+                 device: Optional[torch.device] = None,
+                 deferred_batch_norm: bool = False,
+                 checkpoint: str = 'never',
+                 transport: Optional[Transport] = None,
+                 ) -> None:
+        microbatch_chunks = int(microbatch_chunks)
+        checkpoint = str(checkpoint)
+
+        if balance is None:
+            raise ValueError(recommend_auto_balance('balance is required'))
+        if microbatch_chunks <= 0:
+            raise ValueError('number of chunks must be positive integer')
+        if checkpoint not in ('always', 'except_last', 'never'):
+            raise ValueError("checkpoint is not one of 'always', 'except_last', or 'never'")
+
+        verify_module(module)
+        verify_skippables(module)
+        balance = list(balance)
+        try:
+            check_balance(module, balance)
+        except BalanceError as exc:
+            raise ValueError(recommend_auto_balance(str(exc)))
+
+        # Skip routes are numbered in model order, identically on every rank.
+        stages = [nn.Sequential(s) for s in _stage_slices(module, balance)]
+        layout = inspect_skip_layout(stages)
+        order: Dict[SkipKey, int] = {}
+        for stage in stages:
+            for layer in stage:
+                if isinstance(layer, Skippable):
+                    for key in layer.poppable():
+                        order.setdefault(key, len(order))
+        routes = [(order[(ns, name)], src, dst, (ns, name))
+                  for src, dst, ns, name in layout.cross_routes()]
+        routes.sort()
+        self._routes_out = [(slot, dst, key) for slot, src, dst, key in routes if src == rank]
+        self._routes_in = [(slot, src, key) for slot, src, dst, key in routes if dst == rank]
+
+        partition = get_module_partition(module, rank, balance, device)
+        if deferred_batch_norm:
+            partition = DeferredBatchNorm.convert_deferred_batch_norm(partition, microbatch_chunks)
+        self.module = partition
+
+        self.rank = rank
+        self.world_size = len(workers)
+        self.workers = workers
+        self.chunks = microbatch_chunks
+        self.checkpoint = checkpoint
+        self.device = device
+        self.name = workers[rank]
+        self.balance = balance
+
+        if transport is None:
+            transport = ChannelTransport(workers, rank, type(self))
+        self.transport = transport
+
+        self._outputs: List[Optional[TensorOrTensors]] = [None] * microbatch_chunks
+        self._flights: List[Optional[_Flight]] = [None] * microbatch_chunks
+        self._live = 0      # micro-batches produced by the latest forward()
+
+    # -- topology ----------------------------------------------------------------
+    @property
+    def is_first(self) -> bool:
+        return self.rank == 0
+
+    @property
+    def is_last(self) -> bool:
+        return self.rank == self.world_size - 1
+
+    def _previous_worker(self) -> Optional[str]:
+        return None if self.is_first else self.workers[self.rank - 1]
+
+    def _next_worker(self) -> Optional[str]:
+        return None if self.is_last else self.workers[self.rank + 1]
+
+    def model(self) -> nn.Sequential:
+        """This rank's stage (give its parameters to the local optimiser)."""
+        return self.module
+
+    def _checkpoint_stop(self, m: int) -> int:
+        if not (self.module.training and torch.is_grad_enabled()):
+            return 0
+        return {'always': m, 'except_last': m - 1, 'never': 0}[self.checkpoint]
+
+    # -- forward -------------------------------------------------------------------
+    def _stage_function(self, n_boundary: int, atomic_in: bool, flight: _Flight):
+        routes_in, routes_out = self._routes_in, self._routes_out
+        module = self.module
+
+        def function(inputs: Tensors) -> Tensors:
+            if torch.is_tensor(inputs):
+                inputs = (inputs,)
+            boundary = inputs[:n_boundary]
+            incoming = {key: t for (_, _, key), t in zip(routes_in, inputs[n_boundary:])}
+            tracker = _StageSkipTracker(incoming, [key for _, _, key in routes_out])
+            with use_skip_tracker(tracker):
+                out = module(boundary[0] if atomic_in else tuple(boundary))
+            flight.atomic = torch.is_tensor(out)
+            outs = (out,) if flight.atomic else tuple(out)
+            microbatch.check(outs)
+            flight.n_outputs = len(outs)
+            stashes = []
+            for _, _, key in routes_out:
+                t = tracker.outgoing[key]
+                if t is None:
+                    raise TypeError('None skip tensors cannot cross processes')
+                stashes.append(t)
+            return outs + tuple(stashes)
+
+        return function
+
+    def forward(self, batch: Optional[TensorOrTensors]) -> List[TensorOrTensors]:
+        """Runs every micro-batch through this stage.
+
+        Rank 0 passes the mini-batch; other ranks pass ``None`` and receive
+        their inputs from the previous stage. Returns the list of per
+        micro-batch outputs of *this* stage (the last rank computes one loss
+        per entry and hands the list of losses to :meth:`backward`).
+        """
+        grad_mode = torch.is_grad_enabled()
+        if batch is not None:
+            assert self.is_first, 'only the first stage takes a mini-batch'
+            microbatch.check(batch)
+            pieces = microbatch.scatter(batch, self.chunks)
+            m = len(pieces)
+        else:
+            assert not self.is_first, 'the first stage needs a mini-batch'
+            pieces = None
+            m = self.chunks
+        stop = self._checkpoint_stop(m)
+        tp = self.transport
+
+        self._outputs = [None] * self.chunks
+        self._flights = [None] * self.chunks
+        self._live = m
+
+        for mb in range(m):
+            flight = _Flight()
+            if pieces is not None:
+                received: TensorOrTensors = pieces[mb].value
+            else:
+                received = tp.recv(self.rank - 1, ('fwd', mb, 0))
+            atomic_in = torch.is_tensor(received)
+            moved = to(self.device, received)
+            boundary = tuple(self._as_leaf(t, grad_mode and not self.is_first)
+                             for t in ((moved,) if atomic_in else moved))
+            skips = []
+            for slot, src, _ in self._routes_in:
+                t = tp.recv(src, ('skip', mb, slot))
+                skips.append(self._as_leaf(to(self.device, t), grad_mode))
+
+            leaves = boundary + tuple(skips)
+            flight.leaves = leaves
+            flight.n_boundary = len(boundary)
+            flight.atomic_in = atomic_in
+            function = self._stage_function(len(boundary), atomic_in, flight)
+
+            if mb < stop:
+                chk = Checkpointing(function, Batch(leaves))
+                out_batch = chk.checkpoint()
+                chk.recompute(out_batch)
+                produced = tuple(out_batch)
+            else:
+                produced = function(leaves)
+
+            outs = produced[:flight.n_outputs]
+            stashes = produced[flight.n_outputs:]
+            flight.outputs = produced
+            self._flights[mb] = flight
+            self._outputs[mb] = outs[0] if flight.atomic else outs
+
+            if not self.is_last:
+                tp.send(self.rank + 1, ('fwd', mb, 0),
+                        outs[0].detach() if flight.atomic else tuple(y.detach() for y in outs))
+            for (slot, dst, _), t in zip(self._routes_out, stashes):
+                tp.send(dst, ('skip', mb, slot), t.detach())
+
+        return self._outputs[:m] if m != self.chunks else self._outputs
+
+    @staticmethod
+    def _as_leaf(t: Tensor, grad_mode: bool) -> Tensor:
+        t = t.detach()
+        if grad_mode and t.is_floating_point():
+            t.requires_grad_()
+        return t
+
+    # -- backward ------------------------------------------------------------------
+    def backward(self, losses: Optional[List[Tensor]]) -> None:
+        """Back-propagates every micro-batch (latest first) and passes gradients upstream.
+
+        The last rank passes its per-micro-batch losses; other ranks pass
+        ``None`` and receive output gradients from the next stage.
+        """
+        tp = self.transport
+        if losses is not None:
+            assert self.is_last, 'only the last stage takes losses'
+
+        for mb in reversed(range(self._live)):
+            flight = self._flights[mb]
+            assert flight is not None, 'backward() called before forward()'
+            produced = flight.outputs
+            outs = produced[:flight.n_outputs]
+            stashes = produced[flight.n_outputs:]
+
+            roots: List[Tensor] = []
+            grads: List[Optional[Tensor]] = []
+            if losses is not None:
+                roots.append(losses[mb])
+                grads.append(None)
+            else:
+                received = tp.recv(self.rank + 1, ('bwd', mb, 0),
+                                   like=outs[0] if flight.atomic else outs)
+                received = to(self.device, received)
+                for y, g in zip(outs, (received,) if torch.is_tensor(received) else received):
+                    if y.requires_grad:
+                        roots.append(y)
+                        grads.append(g)
+            for (slot, dst, _), t in zip(self._routes_out, stashes):
+                if not t.is_floating_point():
+                    continue
+                g = tp.recv(dst, ('skip_grad', mb, slot), like=t)
+                if t.requires_grad:
+                    roots.append(t)
+                    grads.append(to(self.device, g))
+
+            if roots:
+                torch.autograd.backward(roots, grads)
+
+            leaves = flight.leaves
+            if not self.is_first:
+                gin = tuple(self._grad_of(x) for x in leaves[:flight.n_boundary])
+                tp.send(self.rank - 1, ('bwd', mb, 0),
+                        gin[0] if flight.atomic_in else gin)
+            for (slot, src, _), x in zip(self._routes_in, leaves[flight.n_boundary:]):
+                if x.is_floating_point():
+                    tp.send(src, ('skip_grad', mb, slot), self._grad_of(x))
+
+            self._flights[mb] = None
+            self._outputs[mb] = None
+
+    @staticmethod
+    def _grad_of(leaf: Tensor) -> Tensor:
+        grad = leaf.grad
+        if grad is None:
+            return torch.zeros_like(leaf)
+        leaf.grad = None
+        return grad
+
+
+class DistributedGPipeDataLoader:
+    """Feeds ``(data, target)`` pairs to the right ranks.
+
+    Rank 0 iterates the real loader, yields ``(data, None)`` and ships each
+    target to the last stage; the last stage yields ``(None, target)``; middle
+    stages yield ``(None, None)``. ``len()`` is ``num_iterations``.
+    Contract: reference ``torchgpipe/distributed/gpipe.py:197-275``.
+
+    With ``transport`` (and ``last_stage_rank``) targets travel through
+    ``torch.distributed``; otherwise through the ``context`` target channel via
+    the ``_put``/``_get`` hooks.
+    """
+
+    @staticmethod
+    def _put(name: str, value: TensorOrTensors) -> None:
+        context.put_target(name, value)
+
+    @staticmethod
+    def _get(name: str) -> TensorOrTensors:
+        return context.get_target(name)
+
+    def __init__(self,
+                 data_loader: Optional[Iterable],
+                 rank: int,
+                 chunks: int,
+                 num_iterations: int,
+                 last_stage: bool,
+                 last_stage_name: str,
+                 *,
+                 transport: Optional[Transport] = None,
+                 last_stage_rank: Optional[int] = None,
+                 ) -> None:
+        self._data_loader = data_loader
+        self._rank = rank
+        self._chunks = chunks
+        self._num_iterations = num_iterations
+        self._last_stage = last_stage
+        self._last_stage_name = last_stage_name
+        self._transport = transport
+        self._last_stage_rank = last_stage_rank
+        self._step = 0
+
+    def _send_target(self, target: TensorOrTensors) -> None:
+        if self._transport is not None and self._last_stage_rank is not None:
+            tensors = (target,) if torch.is_tensor(target) else tuple(target)
+            self._transport.send(self._last_stage_rank, ('target', 0, 0), tensors)
+        else:
+            type(self)._put(self._last_stage_name, target)
+
+    def _recv_target(self) -> TensorOrTensors:
+        if self._transport is not None and self._last_stage_rank is not None:
+            got = self._transport.recv(0, ('target', 0, 0))
+            return got[0] if len(got) == 1 else got
+        return type(self)._get(self._last_stage_name)
+
+    def _first_stage_iter(self) -> Iterator[Tuple[Any, Any]]:
+        assert self._data_loader is not None
+        for (data, target), _ in zip(self._data_loader, range(self._num_iterations)):
+            if self._last_stage:
+                yield (data, target)        # single-stage pipeline
+            else:
+                self._send_target(target)
+                yield (data, None)
+
+    def _last_stage_iter(self) -> Iterator[Tuple[Any, Any]]:
+        for _ in range(self._num_iterations):
+            yield (None, self._recv_target())
+
+    def _middle_stage_iter(self) -> Iterator[Tuple[Any, Any]]:
+        for _ in range(self._num_iterations):
+            yield (None, None)
+
+    def __iter__(self) -> Iterator[Tuple[Any, Any]]:
+        if self._rank == 0:
+            return self._first_stage_iter()
+        if self._last_stage:
+            return self._last_stage_iter()
+        return self._middle_stage_iter()
+
+    def __len__(self) -> int:
+        return self._num_iterations

@@ -1,0 +1,189 @@
+"""Point-to-point transports for the multi-process pipeline.
+
+A transport moves tuples of tensors between stage ranks. Messages are
+identified by ``(kind, micro-batch, slot)`` where ``kind`` is one of
+``'fwd'`` (boundary activations), ``'bwd'`` (boundary gradients), ``'skip'`` /
+``'skip_grad'`` (cross-stage ``@skippable`` tensors, ``slot`` = route index)
+and ``'target'``.
+
+* :class:`ChannelTransport` - in-process queues (the reference's
+  ``context`` channels, ``torchgpipe/distributed/context.py``). Boundary
+  traffic goes through ``DistributedGPipe._put/_get`` so tests can patch them
+  exactly like the reference's tests do.
+* :class:`ProcessGroupTransport` - ``torch.distributed`` send/recv. With the
+  NCCL backend tensors go GPU->GPU over NVLink/NVSwitch and never touch host
+  memory (the reference copies to CPU and pickles through RPC,
+  ``torchgpipe/distributed/gpipe.py:94-96,176-177``). Shapes are announced by
+  a small header the first time a message slot is used and cached afterwards
+  (static shapes per micro-batch index), so steady-state traffic is payload
+  only. For a pair of ranks, both ends issue their operations in the same
+  program order, which is what NCCL point-to-point requires.
+"""
+from collections import defaultdict
+from queue import Queue
+from typing import Any, Dict, List, Optional, Sequence, Tuple, Union
+
+import torch
+from torch import Tensor
+
+__all__ = ['Transport', 'ChannelTransport', 'ProcessGroupTransport']
+
+Key = Tuple[str, int, int]
+Tensors = Tuple[Tensor, ...]
+TensorOrTensors = Union[Tensor, Tensors]
+
+_DTYPES = [torch.float32, torch.float16, torch.bfloat16, torch.float64, torch.int64,
+           torch.int32, torch.int16, torch.int8, torch.uint8, torch.bool]
+_MAX_TENSORS = 8
+_MAX_DIMS = 6
+_HEADER_LEN = 2 + _MAX_TENSORS * (2 + _MAX_DIMS)
+
+
+class Transport:
+    """Interface: ``send`` is asynchronous, ``recv`` returns usable tensors."""
+
+    def send(self, dst: int, key: Key, value: TensorOrTensors) -> None:
+        raise NotImplementedError
+
+    def recv(self, src: int, key: Key, like: Optional[TensorOrTensors] = None,
+             ) -> TensorOrTensors:
+        """Receives a tensor or a tuple of tensors (whichever was sent).
+
+        ``like`` gives the expected shapes/dtypes when the receiver already
+        knows them (gradients mirror the forward tensors)."""
+        raise NotImplementedError
+
+    def flush(self) -> None:
+        """Waits (on the host) until every send issued so far has left this rank."""
+
+
+class ChannelTransport(Transport):
+    """Queues inside one process; ranks are threads (tests) or RPC peers."""
+
+    _extra: Dict[Tuple[str, Key], Queue] = defaultdict(Queue)
+
+    def __init__(self, workers: Dict[int, str], rank: int, owner: Any,
+                 timeout: Optional[float] = None) -> None:
+        self.workers = workers
+        self.rank = rank
+        self.owner = owner          # the DistributedGPipe class (for the _put/_get hooks)
+        self.timeout = timeout
+
+    def send(self, dst: int, key: Key, value: TensorOrTensors) -> None:
+        kind, mb, _ = key
+        name = self.workers[dst]
+        if kind == 'fwd':
+            self.owner._put(name, mb, value, False)
+        elif kind == 'bwd':
+            self.owner._put(name, mb, value, True)
+        else:
+            ChannelTransport._extra[(name, key)].put(value)
+
+    def recv(self, src: int, key: Key, like: Optional[TensorOrTensors] = None,
+             ) -> TensorOrTensors:
+        kind, mb, _ = key
+        name = self.workers[self.rank]
+        if kind == 'fwd':
+            return self.owner._get(name, mb, False)
+        if kind == 'bwd':
+            return self.owner._get(name, mb, True)
+        return ChannelTransport._extra[(name, key)].get(timeout=self.timeout)
+
+
+class ProcessGroupTransport(Transport):
+    """``torch.distributed`` point-to-point (NCCL on GPUs, gloo on CPU)."""
+
+    def __init__(self, device: Optional[torch.device] = None, group: Any = None,
+                 ranks: Optional[Dict[int, int]] = None, static_shapes: bool = True) -> None:
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            raise RuntimeError('torch.distributed must be initialised before creating a '
+                               'ProcessGroupTransport')
+        self.dist = dist
+        self.group = group
+        self.device = device if device is not None else torch.device('cpu')
+        self.ranks = ranks                  # stage rank -> global rank (identity by default)
+        self.static_shapes = static_shapes
+        self._known_send: Dict[Tuple[int, Key], bool] = {}
+        self._known_recv: Dict[Tuple[int, Key], Any] = {}
+        self._pending: List[Any] = []
+
+    def _global(self, stage_rank: int) -> int:
+        return stage_rank if self.ranks is None else self.ranks[stage_rank]
+
+    # -- headers -------------------------------------------------------------
+    def _encode(self, tensors: Sequence[Tensor], atomic: bool) -> Tensor:
+        if len(tensors) > _MAX_TENSORS:
+            raise ValueError(f'at most {_MAX_TENSORS} tensors per message')
+        header = [len(tensors), int(atomic)]
+        for t in tensors:
+            if t.dim() > _MAX_DIMS:
+                raise ValueError(f'at most {_MAX_DIMS} dims per tensor')
+            dims = list(t.shape) + [0] * (_MAX_DIMS - t.dim())
+            header += [_DTYPES.index(t.dtype), t.dim()] + dims
+        header += [0] * (_HEADER_LEN - len(header))
+        return torch.tensor(header, dtype=torch.int64, device=self.device)
+
+    @staticmethod
+    def _decode(header: Tensor) -> Tuple[bool, List[Tuple[torch.dtype, Tuple[int, ...]]]]:
+        values = header.tolist()
+        out = []
+        pos = 2
+        for _ in range(values[0]):
+            dtype = _DTYPES[values[pos]]
+            ndim = values[pos + 1]
+            shape = tuple(values[pos + 2:pos + 2 + ndim])
+            out.append((dtype, shape))
+            pos += 2 + _MAX_DIMS
+        return bool(values[1]), out
+
+    # -- traffic ---------------------------------------------------------------
+    def send(self, dst: int, key: Key, value: TensorOrTensors) -> None:
+        peer = self._global(dst)
+        slot = (dst, key)
+        atomic = torch.is_tensor(value)
+        tensors = (value,) if atomic else tuple(value)
+        if key[0] not in ('bwd', 'skip_grad') and \
+                (not self.static_shapes or slot not in self._known_send):
+            # Gradient messages never need a header: the receiver passes `like`.
+            self._pending.append(self.dist.isend(self._encode(tensors, atomic), peer, group=self.group))
+            self._known_send[slot] = True
+        for t in tensors:
+            t = t.detach()
+            if not t.is_contiguous():
+                t = t.contiguous()
+            self._pending.append(self.dist.isend(t, peer, group=self.group))
+        if len(self._pending) > 4096:
+            self._reap()
+
+    def recv(self, src: int, key: Key, like: Optional[TensorOrTensors] = None,
+             ) -> TensorOrTensors:
+        peer = self._global(src)
+        slot = (src, key)
+        if like is not None:
+            atomic = torch.is_tensor(like)
+            meta = [(t.dtype, tuple(t.shape)) for t in ((like,) if atomic else like)]
+        elif self.static_shapes and slot in self._known_recv:
+            atomic, meta = self._known_recv[slot]
+        else:
+            header = torch.empty(_HEADER_LEN, dtype=torch.int64, device=self.device)
+            self.dist.recv(header, peer, group=self.group)
+            atomic, meta = self._decode(header)
+            self._known_recv[slot] = (atomic, meta)
+        out = []
+        works = []
+        for dtype, shape in meta:
+            buf = torch.empty(shape, dtype=dtype, device=self.device)
+            works.append(self.dist.irecv(buf, peer, group=self.group))
+            out.append(buf)
+        for w in works:
+            w.wait()        # NCCL: orders the current stream behind the transfer
+        return out[0] if atomic else tuple(out)
+
+    def _reap(self) -> None:
+        self._pending = [w for w in self._pending if not w.is_completed()]
+
+    def flush(self) -> None:
+        for w in self._pending:
+            w.wait()
+        self._pending.clear()
