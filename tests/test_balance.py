@@ -1,0 +1,143 @@
+import time
+
+import pytest
+import torch
+from torch import nn
+
+from torchgpipe_b200.balance import balance_by_size, balance_by_time, blockpartition
+from torchgpipe_b200.balance.profile import layerwise_sandbox
+
+
+def test_blockpartition():
+    assert blockpartition.solve([1, 2, 3, 4, 5, 6], partitions=2) == [[1, 2, 3, 4], [5, 6]]
+    assert blockpartition.solve([1, 1, 1, 1], partitions=2) == [[1, 1], [1, 1]]
+    assert blockpartition.solve([5], partitions=1) == [[5]]
+    out = blockpartition.solve([9, 1, 1, 1, 1, 1, 1, 9], partitions=4)
+    assert sum(out, []) == [9, 1, 1, 1, 1, 1, 1, 9] and len(out) == 4
+    assert all(len(b) > 0 for b in out)
+
+
+def test_blockpartition_errors():
+    with pytest.raises(ValueError, match='positive integer'):
+        blockpartition.solve([42], partitions=0)
+    with pytest.raises(ValueError, match='shorter than intended partitions'):
+        blockpartition.solve([42], partitions=2)
+
+
+def test_blockpartition_short_sequence():
+    assert blockpartition.solve([1, 2], partitions=2) == [[1], [2]]
+
+
+def test_balance_by_time_on_cpu():
+    class Delay(nn.Module):
+        def __init__(self, seconds):
+            super().__init__()
+            self.seconds = seconds
+
+        def forward(self, x):
+            time.sleep(self.seconds)
+            return x
+
+    model = nn.Sequential(*[Delay(i / 100) for i in [1, 2, 3, 4, 5, 6]])
+    sample = torch.rand(1)
+    balance = balance_by_time(2, model, sample, device='cpu', timeout=0.5)
+    assert balance == [4, 2]
+
+
+def test_balance_by_time_tuple_io():
+    class Twin(nn.Module):
+        def forward(self, x):
+            return x, x.detach()
+
+    class Add(nn.Module):
+        def forward(self, ab):
+            a, b = ab
+            return a + b
+
+    model = nn.Sequential(Twin(), Add())
+    balance = balance_by_time(1, model, torch.rand(1, requires_grad=True), device='cpu',
+                              timeout=0.05)
+    assert balance == [2]
+
+
+def test_sandbox_leaves_module_untouched():
+    model = nn.Sequential(nn.BatchNorm1d(1))
+    before = {k: v.clone() for k, v in model.state_dict().items()}
+    model.eval()
+    balance_by_time(1, model, torch.rand(8, 1), device='cpu', timeout=0.05)
+    assert not model.training
+    for k, v in model.state_dict().items():
+        assert torch.equal(v, before[k])
+    assert all(p.grad is None for p in model.parameters())
+    clones = list(layerwise_sandbox(model, torch.device('cpu')))
+    assert clones[0] is not model[0] and clones[0].training
+
+
+def test_already_has_grad():
+    model = nn.Sequential(nn.Conv2d(3, 3, 1))
+    model(torch.rand(1, 3, 4, 4)).mean().backward()
+    with pytest.raises(ValueError, match='some parameter already has gradient'):
+        balance_by_time(1, model, torch.rand(1, 3, 4, 4), device='cpu', timeout=0.05)
+
+
+def test_balance_by_size_needs_cuda():
+    with pytest.raises(ValueError, match='only CUDA'):
+        balance_by_size(1, nn.Sequential(nn.Linear(1, 1)), torch.rand(1, 1), device='cpu')
+
+
+def test_deprecated_module_name():
+    with pytest.raises(ImportError, match='balance'):
+        import torchgpipe_balancing  # noqa: F401
+
+
+@pytest.mark.gpu
+def test_balance_by_time_cuda_events():
+    model = nn.Sequential(*[nn.Linear(64, 64) for _ in range(6)])
+    balance = balance_by_time(2, model, torch.rand(32, 64), device='cuda', timeout=0.2)
+    assert sum(balance) == 6 and len(balance) == 2
+
+
+@pytest.mark.gpu
+def test_balance_by_size_latent():
+    class Expand(nn.Module):
+        def __init__(self, times):
+            super().__init__()
+            self.times = times
+
+        def forward(self, x):
+            for _ in range(self.times):
+                x = x + torch.rand_like(x, requires_grad=True)
+            return x
+
+    sample = torch.rand(10, 100, 100)
+    model = nn.Sequential(*[Expand(i) for i in [1, 2, 3, 4, 5, 6]])
+    assert balance_by_size(2, model, sample, device='cuda') == [4, 2]
+    model = nn.Sequential(*[Expand(i) for i in [6, 5, 4, 3, 2, 1]])
+    assert balance_by_size(2, model, sample, device='cuda') == [2, 4]
+
+
+@pytest.mark.gpu
+def test_balance_by_size_param_and_scale():
+    class Tradeoff(nn.Module):
+        def __init__(self, param_size, latent_size):
+            super().__init__()
+            self.fc = nn.Linear(param_size, param_size)
+            self.latent_size = latent_size
+
+        def forward(self, x):
+            for _ in range(self.latent_size):
+                x = x + torch.rand_like(x, requires_grad=True)
+            return x
+
+    model = nn.Sequential(*[nn.Linear(i, i) for i in [10, 20, 30, 40, 50, 60]])
+    assert balance_by_size(2, model, torch.rand(1, 10), param_scale=100, device='cuda',
+                           ) in ([4, 2],)
+    model = nn.Sequential(Tradeoff(param_size=1, latent_size=6),
+                          Tradeoff(param_size=2, latent_size=5),
+                          Tradeoff(param_size=3, latent_size=4),
+                          Tradeoff(param_size=4, latent_size=3),
+                          Tradeoff(param_size=5, latent_size=2),
+                          Tradeoff(param_size=6, latent_size=1))
+    sample = torch.rand(1, requires_grad=True)
+    assert balance_by_size(2, model, sample, param_scale=0, device='cuda') == [2, 4]
+    assert balance_by_size(2, model, sample, param_scale=100, device='cuda') == [4, 2]

@@ -101,6 +101,7 @@ class DeferredBatchNorm(_BatchNorm):
         self.tracked = 0
 
     def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
+        self._check_input_dim(input)
         if not self.training:
             return F.batch_norm(input, self.running_mean, self.running_var,
                                 self.weight, self.bias,
