@@ -1,0 +1,463 @@
+#!/usr/bin/env python
+"""Headline benchmark: U-Net (5,64) training samples/s as an N-stage GPipe pipeline.
+
+Metric and configs are the reference's ``benchmarks/unet-speed`` experiments
+(``/root/reference/benchmarks/unet-speed/main.py:24-68``): ``pipeline-1`` (batch 80,
+2 micro-batches, balance [241]), ``pipeline-2`` (512 / 32 / [104,137]), ``pipeline-4``
+(512 / 16 / [30,66,84,61]), ``pipeline-8`` (640 / 40 / [16,27,31,44,22,57,27,17]);
+input 3x192x192, target ones 1x192x192, BCE-with-logits, SGD(lr=0.1),
+checkpoint='except_last', fp32 storage with TF32 tensor-core convolutions (what cuDNN
+does for the reference under PyTorch defaults).
+
+One step = forward + loss + backward + optimizer.step + zero_grad over one mini-batch.
+
+    python bench.py --gpus 1 --steps 5 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 \
+        --master-port 29511 bench.py --gpus 4 --steps 5 --warmup 3
+    python bench.py --impl reference ...   # the unmodified reference from baseline/_ref
+
+``--impl ours`` (default): this repo. One rank per GPU; for N>1 the stages talk NCCL
+point-to-point (``torchgpipe_b200.distributed``). ``--impl reference``: the reference
+library installed under ``baseline/_ref`` driven through its own public API
+(``torchgpipe.GPipe`` in one process spanning N GPUs - its only packaged multi-GPU mode;
+under torchrun rank 0 drives it and the other ranks only join the barriers).
+
+Rank 0 prints ONE JSON line.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+EXPERIMENTS = {
+    'unet': {
+        1: dict(batch=80, chunks=2, balance=[241]),
+        2: dict(batch=512, chunks=32, balance=[104, 137]),
+        4: dict(batch=512, chunks=16, balance=[30, 66, 84, 61]),
+        8: dict(batch=640, chunks=40, balance=[16, 27, 31, 44, 22, 57, 27, 17]),
+    },
+}
+# Reference's published P40 numbers for the same experiments.
+PUBLISHED = {'unet': {1: 24.456, 2: 35.502, 4: 67.042, 8: 88.497}}
+INPUT_HW = 192
+
+
+# --------------------------------------------------------------------------- helpers
+class ClockSampler:
+    """Samples SM clocks / throttle reasons with nvidia-smi while the timed region runs."""
+
+    QUERY = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+             'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, gpu_index=0):
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.lines = []
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', f'--query-gpu={self.QUERY}', '--format=csv,noheader,nounits',
+                 '-lms', '200', '-i', str(self.gpu_index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except (OSError, ValueError):
+            self.proc = None
+            return
+
+        def pump():
+            assert self.proc is not None and self.proc.stdout is not None
+            for line in self.proc.stdout:
+                self.lines.append(line.strip())
+        self.thread = threading.Thread(target=pump, daemon=True)
+        self.thread.start()
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, sm_max, power = [], [], []
+        reasons = set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for line in self.lines:
+            parts = [p.strip() for p in line.split(',')]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1]))
+                sm_max.append(float(parts[2]))
+                power.append(float(parts[3]))
+            except ValueError:
+                continue
+            for name, flag in zip(names, parts[5:9]):
+                if flag.lower().startswith('active'):
+                    reasons.add(name)
+        if not sm:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['no samples']}
+        # under load = upper half of the samples by power draw
+        order = sorted(range(len(sm)), key=lambda k: power[k])
+        loaded = [sm[k] for k in order[len(order) // 2:]] or sm
+        return {'sm_mhz': statistics.median(loaded), 'sm_max_mhz': max(sm_max),
+                'power_w_max': max(power), 'samples': len(sm), 'reasons': sorted(reasons)}
+
+
+def dist_env():
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', str(rank)))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    return rank, local_rank, world
+
+
+class L2Flusher:
+    """Overwrites a buffer larger than the 126 MB L2 so no step starts with warm lines."""
+
+    def __init__(self, torch, device, mib=256):
+        self.buf = torch.empty(mib * 1024 * 1024 // 4, dtype=torch.float32, device=device)
+
+    def __call__(self):
+        self.buf.zero_()
+
+
+def timed_loop(torch, dist, step_fn, steps, warmup, device, flush, world):
+    """W untimed steps, then exactly K steps between barrier+synchronize, CUDA-event timed."""
+    for _ in range(warmup):
+        step_fn()
+        flush()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    start = torch.cuda.Event(enable_timing=True)
+    end = torch.cuda.Event(enable_timing=True)
+    wall0 = time.perf_counter()
+    start.record(torch.cuda.current_stream(device))
+    for _ in range(steps):
+        step_fn()
+        flush()
+    end.record(torch.cuda.current_stream(device))
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    wall = (time.perf_counter() - wall0) * 1e3
+    ms = start.elapsed_time(end)
+    if world > 1:
+        t = torch.tensor([ms, wall], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, wall = t.tolist()
+    return ms, wall
+
+
+# --------------------------------------------------------------------------- our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import torch.nn.functional as F
+    from torch.optim import SGD
+
+    rank, local_rank, world = dist_env()
+    n = args.gpus
+    cfg = EXPERIMENTS[args.model][n]
+    device = torch.device('cuda', local_rank)
+    torch.cuda.set_device(device)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=device)
+    assert world in (1, n), f'launch with --nproc-per-node {n} (got WORLD_SIZE={world})'
+
+    from torchgpipe_b200 import GPipe
+    from torchgpipe_b200 import ops
+    from torchgpipe_b200.models import unet
+
+    torch.manual_seed(0)
+    model = unet(depth=5, num_convs=5, base_channels=64, input_channels=3, output_channels=1)
+    if not args.no_kernels:
+        model = ops.convert_to_sm100(model)
+
+    batch, chunks, balance = cfg['batch'], cfg['chunks'], cfg['balance']
+    numel_per_sample = INPUT_HW * INPUT_HW
+    host_input = torch.rand(batch, 3, INPUT_HW, INPUT_HW).pin_memory()
+    loss_host = torch.zeros(1).pin_memory()
+
+    first, last = rank == 0, rank == world - 1
+    if world == 1:
+        pipe = GPipe(model, balance, devices=[device] * 1 if n == 1 else
+                     [torch.device('cuda', k) for k in range(n)],
+                     chunks=chunks, checkpoint='except_last')
+        params = list(pipe.parameters())
+        out_device = pipe.devices[-1]
+        dev_input = host_input.to(device)
+        target = torch.ones(batch, 1, INPUT_HW, INPUT_HW, device=out_device)
+
+        def step(inp=None):
+            output = pipe(dev_input if inp is None else inp)
+            loss = F.binary_cross_entropy_with_logits(output, target)
+            loss.backward()
+            opt.step()
+            opt.zero_grad()
+            return loss
+    else:
+        from torchgpipe_b200.distributed import DistributedGPipe, ProcessGroupTransport
+        workers = {r: f'stage{r}' for r in range(world)}
+        tp = ProcessGroupTransport(device)
+        pipe = DistributedGPipe(model, rank, workers, balance, chunks, device=device,
+                                checkpoint='except_last', transport=tp)
+        params = list(pipe.model().parameters())
+        dev_input = host_input.to(device) if first else None
+        target = torch.ones(batch, 1, INPUT_HW, INPUT_HW, device=device) if last else None
+        total = float(batch * numel_per_sample)
+
+        def step(inp=None):
+            outs = pipe.forward((dev_input if inp is None else inp) if first else None)
+            if last:
+                losses = [F.binary_cross_entropy_with_logits(o, t, reduction='sum') / total
+                          for o, t in zip(outs, target.chunk(chunks))]
+                pipe.backward(losses)
+                loss = torch.stack([x.detach() for x in losses]).sum()
+            else:
+                pipe.backward(None)
+                loss = None
+            opt.step()
+            opt.zero_grad()
+            return loss
+
+    opt = SGD(params, lr=0.1)
+    flush = L2Flusher(torch, device)
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ops.reset_launch_count()
+
+    # device-timed, inputs resident on the device
+    if sampler:
+        sampler.start()
+    launches_before = ops.launch_count()
+    # warm-up happens inside timed_loop; count launches over the timed part only
+    for _ in range(args.warmup):
+        step()
+        flush()
+    launches_before = ops.launch_count()
+    ms, _ = timed_loop(torch, dist, lambda: step(), args.steps, 0, device, flush, world)
+    launches = ops.launch_count() - launches_before
+    clocks = sampler.stop() if sampler else None
+
+    # end to end: H2D of the step's input from pinned memory + D2H of the loss, every step
+    stage_in = torch.empty_like(dev_input) if first else None
+
+    def e2e_step():
+        if first:
+            stage_in.copy_(host_input, non_blocking=True)
+        loss = step(stage_in)
+        if loss is not None:
+            loss_host.copy_(loss.detach().reshape(1), non_blocking=False)
+
+    _, e2e_wall = timed_loop(torch, dist, e2e_step, args.steps, 1, device, flush, world)
+
+    if world > 1:
+        t = torch.tensor([float(launches)], device=device, dtype=torch.float64)
+        dist.all_reduce(t)
+        launches = int(t.item())
+
+    samples = batch * args.steps
+    value = samples / (ms / 1e3)
+    e2e_value = samples / (e2e_wall / 1e3)
+    result = {
+        'metric': 'U-Net(5,64) training throughput, GPipe pipeline-%d' % n,
+        'impl': 'ours',
+        'value': value, 'unit': 'samples/s', 'n_gpus': n, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': value / PUBLISHED[args.model][n],
+        'dtype': 'fp32 storage / tf32 tensor-core conv', 'data': 'synthetic',
+        'config': {'model': 'U-Net (B=5,C=64) 241 layers 232.7M params',
+                   'global_batch': batch, 'chunks': chunks, 'balance': balance,
+                   'input': [3, INPUT_HW, INPUT_HW], 'checkpoint': 'except_last',
+                   'optimizer': 'SGD(lr=0.1)', 'loss': 'bce_with_logits',
+                   'parallelism': 'pp%d' % n,
+                   'transport': 'single-process' if world == 1 else 'nccl-p2p',
+                   'l2': 'flushed between steps (256 MiB write)',
+                   'kernels': 'off' if args.no_kernels else 'sm100'},
+        'clocks': clocks,
+        'e2e': {'value': e2e_value, 'unit': 'samples/s',
+                'h2d_bytes_per_step': host_input.numel() * 4, 'd2h_bytes_per_step': 4,
+                'ms_per_step': e2e_wall / args.steps},
+        'gpu_launches': launches,
+    }
+    if rank == 0:
+        print(json.dumps(result), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# --------------------------------------------------------------------------- reference arm
+def run_reference(args):
+    rank, local_rank, world = dist_env()
+    here = os.path.dirname(os.path.abspath(__file__))
+    ref_root = os.path.join(here, 'baseline', '_ref')
+    if not os.path.isdir(os.path.join(ref_root, 'torchgpipe')):
+        if rank == 0:
+            print(json.dumps({'impl': 'reference',
+                              'unavailable': 'baseline/_ref is missing (run '
+                                             'baseline/stage_reference.sh)'}), flush=True)
+        return
+    # Reference first on the path; this repo's package is never imported on this arm.
+    sys.path.insert(0, os.path.join(ref_root, 'benchmarks_models'))
+    sys.path.insert(0, ref_root)
+
+    import torch
+    import torch.distributed as dist
+    import torch.nn.functional as F
+    from torch.optim import SGD
+    import torchgpipe
+    from torchgpipe import GPipe
+    assert os.path.realpath(torchgpipe.__file__).startswith(os.path.realpath(ref_root))
+    from unet import unet  # reference model builder (benchmarks/models/unet)
+
+    n = args.gpus
+    cfg = EXPERIMENTS[args.model][n]
+    device = torch.device('cuda', local_rank)
+    torch.cuda.set_device(device)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=device)
+
+    batch, chunks, balance = cfg['batch'], cfg['chunks'], cfg['balance']
+    driver = rank == 0
+    flush = L2Flusher(torch, device)
+    host_input = torch.rand(batch, 3, INPUT_HW, INPUT_HW).pin_memory()
+    loss_host = torch.zeros(1).pin_memory()
+
+    if driver:
+        torch.manual_seed(0)
+        model = unet(depth=5, num_convs=5, base_channels=64, input_channels=3, output_channels=1)
+        devices = [torch.device('cuda', k) for k in range(n)]
+        pipe = GPipe(model, balance, devices=devices, chunks=chunks)   # checkpoint default
+        opt = SGD(pipe.parameters(), lr=0.1)
+        dev_input = host_input.to(devices[0])
+        target = torch.ones(batch, 1, INPUT_HW, INPUT_HW, device=devices[-1])
+        stage_in = torch.empty_like(dev_input)
+
+        def step(inp=None):
+            output = pipe(dev_input if inp is None else inp)
+            loss = F.binary_cross_entropy_with_logits(output, target)
+            loss.backward()
+            opt.step()
+            opt.zero_grad()
+            return loss
+
+        def sync_all():
+            for d in devices:
+                torch.cuda.synchronize(d)
+    else:
+        def step(inp=None):
+            return None
+
+        def sync_all():
+            torch.cuda.synchronize()
+
+    def timed(step_fn, steps, warmup):
+        for _ in range(warmup):
+            step_fn()
+            flush()
+        sync_all()
+        if world > 1:
+            dist.barrier()
+        sync_all()
+        ms = 0.0
+        wall0 = time.perf_counter()
+        if driver:
+            # one event pair per pipeline device; the step is done when the slowest is done
+            starts = [torch.cuda.Event(enable_timing=True) for _ in devices]
+            ends = [torch.cuda.Event(enable_timing=True) for _ in devices]
+            for d, e in zip(devices, starts):
+                e.record(torch.cuda.current_stream(d))
+        for _ in range(steps):
+            step_fn()
+            flush()
+        if driver:
+            for d, e in zip(devices, ends):
+                e.record(torch.cuda.current_stream(d))
+        sync_all()
+        if world > 1:
+            dist.barrier()
+        wall = (time.perf_counter() - wall0) * 1e3
+        if driver:
+            ms = max(s.elapsed_time(e) for s, e in zip(starts, ends))
+            # stages start at different times: the device-side span cannot be shorter than
+            # the longest single-device span; wall bounds it from above.
+        if world > 1:
+            t = torch.tensor([ms, wall], device=device, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, wall = t.tolist()
+        return ms, wall
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ms, _ = timed(lambda: step(), args.steps, args.warmup)
+    clocks = sampler.stop() if sampler else None
+
+    def e2e_step():
+        if driver:
+            stage_in.copy_(host_input, non_blocking=True)
+            loss = step(stage_in)
+            loss_host.copy_(loss.detach().reshape(1).to('cpu'))
+
+    _, e2e_wall = timed(e2e_step, args.steps, 1)
+
+    samples = batch * args.steps
+    value = samples / (ms / 1e3)
+    result = {
+        'metric': 'U-Net(5,64) training throughput, GPipe pipeline-%d' % n,
+        'impl': 'reference',
+        'value': value, 'unit': 'samples/s', 'n_gpus': n, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': value / PUBLISHED[args.model][n],
+        'dtype': 'fp32 storage / tf32 cuDNN conv (PyTorch defaults)', 'data': 'synthetic',
+        'config': {'model': 'U-Net (B=5,C=64) 241 layers 232.7M params',
+                   'global_batch': batch, 'chunks': chunks, 'balance': balance,
+                   'input': [3, INPUT_HW, INPUT_HW], 'checkpoint': 'except_last',
+                   'optimizer': 'SGD(lr=0.1)', 'loss': 'bce_with_logits',
+                   'parallelism': 'pp%d' % n, 'transport': 'single-process (reference GPipe)',
+                   'l2': 'flushed between steps (256 MiB write)',
+                   'torchgpipe': torchgpipe.__version__},
+        'clocks': clocks,
+        'e2e': {'value': samples / (e2e_wall / 1e3), 'unit': 'samples/s',
+                'h2d_bytes_per_step': host_input.numel() * 4, 'd2h_bytes_per_step': 4,
+                'ms_per_step': e2e_wall / args.steps},
+        'gpu_launches': 0,
+    }
+    if rank == 0:
+        print(json.dumps(result), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    p = argparse.ArgumentParser()
+    p.add_argument('--gpus', type=int, default=1)
+    p.add_argument('--steps', type=int, default=5)
+    p.add_argument('--warmup', type=int, default=3)
+    p.add_argument('--impl', choices=['ours', 'reference'], default='ours')
+    p.add_argument('--model', choices=['unet'], default='unet')
+    p.add_argument('--no-kernels', action='store_true',
+                   help='ours arm: keep torch/cuDNN ops (diagnostic; not the product path)')
+    args = p.parse_args()
+    if args.gpus not in EXPERIMENTS[args.model]:
+        raise SystemExit('--gpus must be one of %s' % sorted(EXPERIMENTS[args.model]))
+    if args.impl == 'reference':
+        try:
+            run_reference(args)
+        except ImportError as exc:
+            print(json.dumps({'impl': 'reference', 'unavailable': f'import failed: {exc}'}))
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,400 @@
+// Implicit-GEMM 2-D convolution forward (stride 1) for sm_100a: tcgen05.mma (TF32 in, FP32
+// accumulate in TMEM), operands staged by TMA, NHWC activations, KRSC weights.
+//
+//   Y[n,ho,wo,k] = sum_{r,s,c} X[n, ho+r-pad_h, wo+s-pad_w, c] * Wt[k,r,s,c]
+//
+// GEMM view: M = N*Ho*Wo output pixels, N = K output channels, reduction = R*S*C.
+// One CTA tile = 128 output pixels arranged as a BW x BH x BNB box of (w, h, n) x BN channels.
+// For every filter tap (r,s) and every 32-channel block the A operand is ONE 4-D TMA box of the
+// input shifted by the tap offset; pixels outside the image are zero-filled by TMA, which is
+// exactly the convolution's zero padding - no im2col buffer, no index arithmetic on the SM.
+// The same kernel computes the data gradient of a stride-1 convolution when it is given dY, the
+// tap-flipped / channel-transposed weights and pad' = R-1-pad.
+//
+// Warp roles (256 threads, 1 CTA per SM, persistent over tiles):
+//   warp 0   TMA producer            (one elected lane)
+//   warp 1   tcgen05.mma issuer      (one elected lane)
+//   warp 2   TMEM allocator
+//   warps 4-7 epilogue: TMEM -> registers -> swizzled smem -> TMA store, plus optional fused
+//            per-channel (BatchNorm) or per-(image, channel) (InstanceNorm) sum / sum-of-squares
+//            so the normalisation that follows never has to re-read Y for its statistics.
+// Pipelines: smem full/empty ring (TMA <-> MMA) and a 2-deep TMEM accumulator ring
+// (MMA <-> epilogue) so the epilogue of tile t overlaps the main loop of tile t+1.
+//
+// Covers reference call sites: every nn.Conv2d of benchmarks/models/{unet,resnet,amoebanet}
+// with stride 1 (forward: K1; backward-data: K2 in SURVEY 2.3b).
+#include "sm100_ptx.cuh"
+#include "tensormap.h"
+#include "tgb_internal.h"
+
+namespace tgb {
+
+constexpr int kBlockM = 128;        // UMMA M
+constexpr int kBlockKBytes = 128;   // one swizzle row: 32 fp32
+constexpr int kBlockK = 32;
+constexpr int kUmmaK = 8;           // tf32: 32 bytes per MMA
+constexpr int kEpiChunk = 32;       // columns per epilogue chunk (= one 128B row of Y)
+constexpr int kThreads = 256;
+
+struct ConvGeom {
+  int N, H, W, C, K;
+  int R, S, pad_h, pad_w;
+  int Ho, Wo;
+  int BW, BH, BNB;                  // pixel box; rows_valid = BW*BH*BNB <= 128
+  int tiles_w, tiles_h, tiles_n, tiles_k;
+  int c_blocks;
+  int stats_mode;                   // 0 none, 1 per (n,k), 2 per k
+};
+
+template <int BN, int STAGES>
+struct SmemLayout {
+  static constexpr int kABytes = kBlockM * kBlockKBytes;       // 16 KB
+  static constexpr int kBBytes = BN * kBlockKBytes;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kEpiBytes = kBlockM * kBlockKBytes;     // 16 KB per staging buffer
+  static constexpr int kEpiOffset = STAGES * kStageBytes;
+  static constexpr int kBarOffset = kEpiOffset + 2 * kEpiBytes;
+  static constexpr int kTotal = kBarOffset + (2 * STAGES + 4) * 8 + 16;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
+                       const __grid_constant__ CUtensorMap tmap_w,
+                       const __grid_constant__ CUtensorMap tmap_y,
+                       const ConvGeom g, float* __restrict__ stats) {
+  using L = SmemLayout<BN, STAGES>;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // dynamic smem is only guaranteed 16B aligned: round up to the 1024B the swizzle needs
+  uint8_t* smem = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full = empty_bar + STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int rows_valid = g.BW * g.BH * g.BNB;
+  const int num_tiles = g.tiles_w * g.tiles_h * g.tiles_n * g.tiles_k;
+  const int k_iters = g.R * g.S * g.c_blocks;
+  const uint32_t stage_tx = static_cast<uint32_t>(rows_valid * kBlockKBytes + L::kBBytes);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_w);
+    tma_prefetch_desc(&tmap_y);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 4);       // one arrival per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 2 * BN);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  auto decode_tile = [&](int tile, int& kt, int& tw, int& th, int& tn) {
+    kt = tile % g.tiles_k;
+    int rest = tile / g.tiles_k;
+    tw = rest % g.tiles_w;
+    rest /= g.tiles_w;
+    th = rest % g.tiles_h;
+    tn = rest / g.tiles_h;
+  };
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int kt, tw, th, tn;
+        decode_tile(tile, kt, tw, th, tn);
+        const int w0 = tw * g.BW - g.pad_w;
+        const int h0 = th * g.BH - g.pad_h;
+        const int n0 = tn * g.BNB;
+        const int k0 = kt * BN;
+        for (int tap = 0; tap < g.R * g.S; ++tap) {
+          const int r = tap / g.S;
+          const int s = tap - r * g.S;
+          for (int cb = 0; cb < g.c_blocks; ++cb) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            uint8_t* a_dst = smem + stage * L::kStageBytes;
+            uint8_t* b_dst = a_dst + L::kABytes;
+            mbar_expect_tx(&full_bar[stage], stage_tx);
+            tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cb * kBlockK, w0 + s, h0 + r, n0);
+            tma_load_4d(b_dst, &tmap_w, &full_bar[stage], cb * kBlockK, tap, k0, 0);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer
+    constexpr uint32_t idesc = make_idesc(/*tf32*/ 2, kBlockM, BN, 0, 0);
+    // One thread waits, issues and commits: tcgen05.commit tracks the MMAs of the issuing thread.
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int it = 0; it < k_iters; ++it) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
+          const uint32_t b_addr = a_addr + L::kABytes;
+          const uint64_t a_desc = make_smem_desc_sw128(a_addr, 16, 1024);
+          const uint64_t b_desc = make_smem_desc_sw128(b_addr, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            // advance 32 bytes inside the 128B swizzle row: +2 in the (addr >> 4) field
+            mma_tf32_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc,
+                        (it > 0 || k > 0) ? 1u : 0u);
+          }
+          mma_commit(&empty_bar[stage]);                  // smem slot free once MMAs retire
+          if (it == k_iters - 1) mma_commit(&tmem_full[acc]);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------ epilogue
+    const int q = warp - 4;                       // TMEM lane quarter of this warp
+    const int row = q * 32 + lane;                // tile row owned by this thread
+    const int epi_tid = threadIdx.x - 128;
+    uint8_t* epi = smem + L::kEpiOffset;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    int chunk_counter = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int kt, tw, th, tn;
+      decode_tile(tile, kt, tw, th, tn);
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+#pragma unroll 1
+      for (int j = 0; j < BN / kEpiChunk; ++j, ++chunk_counter) {
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + static_cast<uint32_t>(acc * BN + j * kEpiChunk) +
+                               (static_cast<uint32_t>(q * 32) << 16);
+        tmem_ld_32x32(taddr, v);
+        tmem_ld_wait();
+        if (j == BN / kEpiChunk - 1) {
+          // accumulator fully read: hand the TMEM stage back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        }
+        uint8_t* buf = epi + (chunk_counter & 1) * L::kEpiBytes;
+        // the TMA store issued two chunks ago read from this buffer: wait for it
+        if (epi_tid == 0) tma_store_wait_read<1>();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        {
+          // row-major [128 rows][128 B] with the 128B swizzle TMA expects:
+          // 16-byte chunk c of row r lives at chunk (c ^ (r & 7))
+          uint8_t* rowp = buf + row * kBlockKBytes;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const int pc = c ^ (row & 7);
+            *reinterpret_cast<uint4*>(rowp + pc * 16) =
+                make_uint4(v[4 * c + 0], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+          }
+        }
+        fence_proxy_async_smem();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (epi_tid == 0) {
+          tma_store_4d(&tmap_y, buf, kt * BN + j * kEpiChunk, tw * g.BW, th * g.BH,
+                       tn * g.BNB);
+          tma_store_commit();
+        }
+        if (g.stats_mode != 0) {
+          // column sums over this warp's 32 rows, read back from the staging buffer:
+          // lane = column, so each LDS hits 32 distinct words of one 128B row (no conflicts)
+          const int col = lane;
+          const int kglob = kt * BN + j * kEpiChunk + col;
+          const int pix_per_img = g.BW * g.BH;
+          float s1 = 0.f, s2 = 0.f;
+          int cur_img = -1;
+          for (int rr = 0; rr < 32; ++rr) {
+            const int r2 = q * 32 + rr;
+            if (r2 >= rows_valid) break;
+            // rows of a partial tile that fall outside the output contribute nothing
+            const int ww = r2 % g.BW;
+            const int hh = (r2 / g.BW) % g.BH;
+            const int nn = r2 / pix_per_img;
+            if (tw * g.BW + ww >= g.Wo || th * g.BH + hh >= g.Ho || tn * g.BNB + nn >= g.N)
+              continue;
+            const int img = (g.stats_mode == 1) ? (tn * g.BNB + nn) : 0;
+            if (img != cur_img) {
+              if (cur_img >= 0 && cur_img < g.N && kglob < g.K) {
+                float* dst = stats + (static_cast<size_t>(cur_img) * g.K + kglob) * 2;
+                atomicAdd(dst, s1);
+                atomicAdd(dst + 1, s2);
+              }
+              cur_img = img;
+              s1 = 0.f;
+              s2 = 0.f;
+            }
+            const int pc = (col >> 2) ^ (r2 & 7);
+            const float x = *reinterpret_cast<const float*>(buf + r2 * kBlockKBytes + pc * 16 +
+                                                            (col & 3) * 4);
+            s1 += x;
+            s2 = fmaf(x, x, s2);
+          }
+          if (cur_img >= 0 && cur_img < g.N && kglob < g.K) {
+            float* dst = stats + (static_cast<size_t>(cur_img) * g.K + kglob) * 2;
+            atomicAdd(dst, s1);
+            atomicAdd(dst + 1, s2);
+          }
+        }
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+    if (epi_tid == 0) tma_store_wait_all<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * BN);
+  }
+}
+
+// ---------------------------------------------------------------- host side
+static void choose_pixel_box(int N, int Ho, int Wo, int& BW, int& BH, int& BNB) {
+  // Largest-utilisation box with BW*BH*BNB <= 128 that wastes the fewest rows on partial tiles.
+  double best = -1.0;
+  BW = 1; BH = 1; BNB = 1;
+  for (int bw = 1; bw <= Wo && bw <= 128; ++bw) {
+    for (int bh = 1; bh <= Ho && bw * bh <= 128; ++bh) {
+      int max_nb = 128 / (bw * bh);
+      // only batch several images into a tile when the tile already covers a whole image
+      int nb_hi = (bw == Wo && bh == Ho) ? max_nb : 1;
+      for (int nb = 1; nb <= nb_hi && nb <= N; ++nb) {
+        const long tiles = static_cast<long>((Wo + bw - 1) / bw) * ((Ho + bh - 1) / bh) *
+                           ((N + nb - 1) / nb);
+        const double useful = static_cast<double>(N) * Ho * Wo / (static_cast<double>(tiles) * 128);
+        // prefer wide boxes (longer contiguous runs per TMA row) on ties
+        const double score = useful + 1e-6 * bw;
+        if (score > best) {
+          best = score;
+          BW = bw; BH = bh; BNB = nb;
+        }
+      }
+    }
+  }
+}
+
+template <int BN, int STAGES>
+static int launch_fprop(const CUtensorMap& mx, const CUtensorMap& mw, const CUtensorMap& my,
+                        const ConvGeom& g, float* stats, int sm_count, cudaStream_t stream) {
+  using L = SmemLayout<BN, STAGES>;
+  constexpr int smem_bytes = L::kTotal + 1024;      // + alignment slack
+  static bool configured = false;
+  auto kern = conv_fprop_tf32_kernel<BN, STAGES>;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         smem_bytes);
+    if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(conv_fprop): %s",
+                                           cudaGetErrorString(e));
+    configured = true;
+  }
+  const int num_tiles = g.tiles_w * g.tiles_h * g.tiles_n * g.tiles_k;
+  const int grid = num_tiles < sm_count ? num_tiles : sm_count;
+  kern<<<grid, kThreads, smem_bytes, stream>>>(mx, mw, my, g, stats);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_error("conv_fprop launch: %s", cudaGetErrorString(e));
+  count_launch();
+  return 0;
+}
+
+}  // namespace tgb
+
+using namespace tgb;
+
+extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, float* stats,
+                                     int N, int H, int W, int C, int K, int R, int S, int pad_h,
+                                     int pad_w, int stats_mode, cudaStream_t stream) {
+  if (C % 4 != 0 || K % 32 != 0)
+    return set_error("conv_fprop: need C %% 4 == 0 and K %% 32 == 0 (got C=%d K=%d)", C, K);
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) |
+       reinterpret_cast<uintptr_t>(y)) & 15)
+    return set_error("conv_fprop: tensors must be 16-byte aligned");
+  ConvGeom g;
+  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K;
+  g.R = R; g.S = S; g.pad_h = pad_h; g.pad_w = pad_w;
+  g.Ho = H + 2 * pad_h - R + 1;
+  g.Wo = W + 2 * pad_w - S + 1;
+  if (g.Ho <= 0 || g.Wo <= 0) return set_error("conv_fprop: empty output");
+  choose_pixel_box(N, g.Ho, g.Wo, g.BW, g.BH, g.BNB);
+  const int BN = (K % 256 == 0) ? 256 : (K % 128 == 0) ? 128 : (K % 64 == 0) ? 64 : 32;
+  g.tiles_w = (g.Wo + g.BW - 1) / g.BW;
+  g.tiles_h = (g.Ho + g.BH - 1) / g.BH;
+  g.tiles_n = (N + g.BNB - 1) / g.BNB;
+  g.tiles_k = K / BN;
+  g.c_blocks = (C + kBlockK - 1) / kBlockK;
+  g.stats_mode = stats ? stats_mode : 0;
+
+  CUtensorMap mx, mw, my;
+  {
+    uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    uint64_t strides[3] = {(uint64_t)C * 4, (uint64_t)W * C * 4, (uint64_t)H * W * C * 4};
+    uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
+    if (make_tensor_map(&mx, x, 4, 4, dims, strides, box, true))
+      return set_error("conv_fprop: tensor map for X failed");
+  }
+  {
+    // weights [K][R*S][C] viewed as a 3-D (4-D with a unit dim) tensor so that a partial last
+    // channel block is zero-filled instead of bleeding into the next tap
+    uint64_t dims[4] = {(uint64_t)C, (uint64_t)(R * S), (uint64_t)K, 1};
+    uint64_t strides[3] = {(uint64_t)C * 4, (uint64_t)R * S * C * 4, (uint64_t)K * R * S * C * 4};
+    uint32_t box[4] = {32, 1, (uint32_t)BN, 1};
+    if (make_tensor_map(&mw, w, 4, 4, dims, strides, box, true))
+      return set_error("conv_fprop: tensor map for W failed");
+  }
+  {
+    uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)N};
+    uint64_t strides[3] = {(uint64_t)K * 4, (uint64_t)g.Wo * K * 4,
+                           (uint64_t)g.Ho * g.Wo * K * 4};
+    uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
+    if (make_tensor_map(&my, y, 4, 4, dims, strides, box, true))
+      return set_error("conv_fprop: tensor map for Y failed");
+  }
+  const int sms = sm_count();
+  switch (BN) {
+    case 256: return launch_fprop<256, 4>(mx, mw, my, g, stats, sms, stream);
+    case 128: return launch_fprop<128, 6>(mx, mw, my, g, stats, sms, stream);
+    case 64:  return launch_fprop<64, 8>(mx, mw, my, g, stats, sms, stream);
+    default:  return launch_fprop<32, 8>(mx, mw, my, g, stats, sms, stream);
+  }
+}
