@@ -1,0 +1,403 @@
+// Weight gradient of a stride-1 2-D convolution for sm_100a (tcgen05, TF32 -> FP32 in TMEM).
+//
+//   dW[k,r,s,c] = sum_{n,ho,wo} dY[n,ho,wo,k] * X[n, ho+r-pad_h, wo+s-pad_w, c]
+//
+// GEMM view per filter tap: M = K (output channels), N = C (input channels), and the reduction
+// runs over all N*Ho*Wo output pixels. In NHWC memory the reduction index is the *outer*
+// dimension of both operands, so both are fed to the tensor core as MN-major (transposed)
+// operands straight from the TMA boxes: a box of P pixels x 32 channels with the 128-byte
+// swizzle IS the canonical MN-major SWIZZLE_128B layout ((4,8,m),(8,k)):((1,4,LBO),(32,SBO))
+// (fp32 elements), with one MMA (K=8) consuming one 8-pixel swizzle atom of every channel chunk.
+// The X box is shifted by the tap offset and zero-filled outside the image by TMA (= padding).
+//
+// Work item = (k-tile of 128, c-tile of BN, tap, split of the pixel range); persistent CTAs.
+// Small-channel layers have millions of pixels and few (k,c,tap) tiles, so the pixel range is
+// split across CTAs; each split writes an fp32 partial into scratch and a second kernel adds
+// the partials in a fixed order (deterministic, no atomics). Large-channel layers use 1 split
+// and store dW directly.
+//
+// Reference call site: autograd of every nn.Conv2d (cuDNN in the reference).
+#include "sm100_ptx.cuh"
+#include "tensormap.h"
+#include "tgb_internal.h"
+
+namespace tgb {
+
+constexpr int kWgThreads = 256;
+constexpr int kWgM = 128;
+constexpr int kWgChunkBytes = 4096;      // 32 pixels x 128 B: one channel chunk of one stage
+constexpr int kWgMaxPix = 32;
+
+struct WgradGeom {
+  int N, H, W, C, K;
+  int R, S, pad_h, pad_w;
+  int Ho, Wo;
+  int BW, BH, BNB, P;                    // pixel box, P = BW*BH*BNB (multiple of 8, <= 32)
+  int tiles_w, tiles_h, tiles_n;         // pixel blocks
+  int k_tiles, c_tiles, splits;
+  int blocks_per_split;
+};
+
+template <int BN, int STAGES>
+struct WgSmem {
+  static constexpr int kABytes = 4 * kWgChunkBytes;
+  static constexpr int kBBytes = (BN / 32) * kWgChunkBytes;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBarOffset = STAGES * kStageBytes;
+  static constexpr int kTotal = kBarOffset + (2 * STAGES + 4) * 8 + 16;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kWgThreads, 1)
+conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmap_dy,
+                       const __grid_constant__ CUtensorMap tmap_x, const WgradGeom g,
+                       float* __restrict__ out) {
+  using L = WgSmem<BN, STAGES>;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full = empty_bar + STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int taps = g.R * g.S;
+  const int num_items = g.k_tiles * g.c_tiles * taps * g.splits;
+  const int total_blocks = g.tiles_w * g.tiles_h * g.tiles_n;
+  const uint32_t stage_tx = static_cast<uint32_t>((4 + BN / 32) * g.P * 128);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_dy);
+    tma_prefetch_desc(&tmap_x);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 2 * BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // item -> (kt, ct, tap, split); kt fastest so concurrent CTAs share the X boxes in L2
+  auto decode = [&](int item, int& kt, int& ct, int& tap, int& split) {
+    kt = item % g.k_tiles;
+    int rest = item / g.k_tiles;
+    ct = rest % g.c_tiles;
+    rest /= g.c_tiles;
+    tap = rest % taps;
+    split = rest / taps;
+  };
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        int kt, ct, tap, split;
+        decode(item, kt, ct, tap, split);
+        const int r = tap / g.S, s = tap - r * g.S;
+        const int b_begin = split * g.blocks_per_split;
+        const int b_end = min(total_blocks, b_begin + g.blocks_per_split);
+        for (int blk = b_begin; blk < b_end; ++blk) {
+          const int tw = blk % g.tiles_w;
+          const int rest = blk / g.tiles_w;
+          const int th = rest % g.tiles_h;
+          const int tn = rest / g.tiles_h;
+          const int w0 = tw * g.BW, h0 = th * g.BH, n0 = tn * g.BNB;
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* a_dst = smem + stage * L::kStageBytes;
+          uint8_t* b_dst = a_dst + L::kABytes;
+          mbar_expect_tx(&full_bar[stage], stage_tx);
+#pragma unroll
+          for (int ch = 0; ch < 4; ++ch)
+            tma_load_4d(a_dst + ch * kWgChunkBytes, &tmap_dy, &full_bar[stage],
+                        kt * kWgM + ch * 32, w0, h0, n0);
+#pragma unroll
+          for (int ch = 0; ch < BN / 32; ++ch)
+            tma_load_4d(b_dst + ch * kWgChunkBytes, &tmap_x, &full_bar[stage],
+                        ct * BN + ch * 32, w0 + s - g.pad_w, h0 + r - g.pad_h, n0);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc(/*tf32*/ 2, kWgM, BN, /*a MN-major*/ 1, /*b*/ 1);
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      const int k_steps = g.P / 8;
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        int kt, ct, tap, split;
+        decode(item, kt, ct, tap, split);
+        const int b_begin = split * g.blocks_per_split;
+        const int b_end = min(total_blocks, b_begin + g.blocks_per_split);
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        bool first = true;
+        for (int blk = b_begin; blk < b_end; ++blk) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
+          const uint32_t b_addr = a_addr + L::kABytes;
+          // MN-major SW128: LBO = stride between 32-channel chunks, SBO = between 8-pixel atoms
+          const uint64_t a_desc = make_smem_desc_sw128(a_addr, kWgChunkBytes, 1024);
+          const uint64_t b_desc = make_smem_desc_sw128(b_addr, kWgChunkBytes, 1024);
+          for (int k = 0; k < k_steps; ++k) {
+            // next 8 pixels = next 1024-byte swizzle atom: +64 in the (addr >> 4) field
+            mma_tf32_ss(d_tmem, a_desc + 64 * k, b_desc + 64 * k, idesc, first ? 0u : 1u);
+            first = false;
+          }
+          mma_commit(&empty_bar[stage]);
+          if (blk == b_end - 1) mma_commit(&tmem_full[acc]);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        if (b_begin >= b_end) {
+          // empty split (cannot happen with the host's split choice, but never deadlock)
+          mma_commit(&tmem_full[acc]);
+        }
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    const int q = warp - 4;
+    const int row = q * 32 + lane;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const size_t tap_stride = static_cast<size_t>(g.C);
+    const size_t k_stride = static_cast<size_t>(taps) * g.C;
+    const size_t split_stride = static_cast<size_t>(g.K) * k_stride;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      int kt, ct, tap, split;
+      decode(item, kt, ct, tap, split);
+      const int b_begin = split * g.blocks_per_split;
+      const bool empty = b_begin >= min(total_blocks, b_begin + g.blocks_per_split);
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const int kglob = kt * kWgM + row;
+      float* dst_row = out + split * split_stride + static_cast<size_t>(kglob) * k_stride +
+                       tap * tap_stride + static_cast<size_t>(ct) * BN;
+#pragma unroll 1
+      for (int j = 0; j < BN / 32; ++j) {
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + static_cast<uint32_t>(acc * BN + j * 32) +
+                               (static_cast<uint32_t>(q * 32) << 16);
+        tmem_ld_32x32(taddr, v);
+        tmem_ld_wait();
+        if (kglob < g.K) {
+          const int c_base = ct * BN + j * 32;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            if (c_base + c * 4 < g.C) {
+              float4 o = empty ? make_float4(0, 0, 0, 0)
+                               : make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]),
+                                             __uint_as_float(v[4 * c + 2]),
+                                             __uint_as_float(v[4 * c + 3]));
+              *reinterpret_cast<float4*>(dst_row + j * 32 + c * 4) = o;
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * BN);
+  }
+}
+
+// out[i] = sum_s partial[s][i] (fixed order), optionally accumulated onto out (beta = 1)
+__global__ void wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out,
+                                    size_t n4, int splits, size_t split_stride4, int accumulate) {
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    float4 acc = accumulate ? reinterpret_cast<const float4*>(out)[i] : make_float4(0, 0, 0, 0);
+    for (int s = 0; s < splits; ++s) {
+      const float4 v = reinterpret_cast<const float4*>(partial)[s * split_stride4 + i];
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    reinterpret_cast<float4*>(out)[i] = acc;
+  }
+}
+
+static void choose_wgrad_box(int N, int Ho, int Wo, int& BW, int& BH, int& BNB) {
+  double best = -1.0;
+  BW = 8; BH = 1; BNB = 1;
+  for (int bw = 1; bw <= Wo && bw <= kWgMaxPix; ++bw)
+    for (int bh = 1; bh <= Ho && bw * bh <= kWgMaxPix; ++bh) {
+      const int nb_hi = (bw == Wo && bh == Ho) ? kWgMaxPix / (bw * bh) : 1;
+      for (int nb = 1; nb <= nb_hi && nb <= N; ++nb) {
+        const int p = bw * bh * nb;
+        if (p % 8) continue;
+        const double blocks = static_cast<double>((Wo + bw - 1) / bw) * ((Ho + bh - 1) / bh) *
+                              ((N + nb - 1) / nb);
+        const double useful = static_cast<double>(N) * Ho * Wo / (blocks * p);
+        // fewer, fuller stages win: utilisation first, then box size, then width
+        const double score = useful * (0.75 + 0.25 * p / kWgMaxPix) + 1e-6 * bw;
+        if (score > best) {
+          best = score;
+          BW = bw; BH = bh; BNB = nb;
+        }
+      }
+    }
+}
+
+template <int BN, int STAGES>
+static int launch_wgrad(const CUtensorMap& mdy, const CUtensorMap& mx, const WgradGeom& g,
+                        float* out, int grid, cudaStream_t stream) {
+  using L = WgSmem<BN, STAGES>;
+  constexpr int smem_bytes = L::kTotal + 1024;
+  static bool configured = false;
+  auto kern = conv_wgrad_tf32_kernel<BN, STAGES>;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         smem_bytes);
+    if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(conv_wgrad): %s",
+                                           cudaGetErrorString(e));
+    configured = true;
+  }
+  kern<<<grid, kWgThreads, smem_bytes, stream>>>(mdy, mx, g, out);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_error("conv_wgrad launch: %s", cudaGetErrorString(e));
+  count_launch();
+  return 0;
+}
+
+// Fills the geometry and the number of splits for a problem; shared by the planning query and
+// the launcher so both always agree.
+static int plan_wgrad(int N, int H, int W, int C, int K, int R, int S, int pad_h, int pad_w,
+                      WgradGeom& g, int& BN) {
+  if (C % 4 != 0 || K % 4 != 0) return set_error("conv_wgrad: need C %% 4 == 0 and K %% 4 == 0");
+  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K;
+  g.R = R; g.S = S; g.pad_h = pad_h; g.pad_w = pad_w;
+  g.Ho = H + 2 * pad_h - R + 1;
+  g.Wo = W + 2 * pad_w - S + 1;
+  if (g.Ho <= 0 || g.Wo <= 0) return set_error("conv_wgrad: empty output");
+  choose_wgrad_box(N, g.Ho, g.Wo, g.BW, g.BH, g.BNB);
+  g.P = g.BW * g.BH * g.BNB;
+  g.tiles_w = (g.Wo + g.BW - 1) / g.BW;
+  g.tiles_h = (g.Ho + g.BH - 1) / g.BH;
+  g.tiles_n = (N + g.BNB - 1) / g.BNB;
+  const int c32 = (C + 31) / 32 * 32;
+  BN = c32 >= 256 ? 256 : c32 >= 128 ? 128 : c32 >= 64 ? 64 : 32;
+  g.k_tiles = (K + kWgM - 1) / kWgM;
+  g.c_tiles = (C + BN - 1) / BN;
+  const int items = g.k_tiles * g.c_tiles * R * S;
+  const int total_blocks = g.tiles_w * g.tiles_h * g.tiles_n;
+  const int sms = sm_count();
+  int splits = 1;
+  if (items < sms) {
+    splits = (sms + items - 1) / items;
+    // keep at least 8 pixel blocks per split so the prologue/epilogue stay amortised
+    const int max_splits = total_blocks / 8 > 0 ? total_blocks / 8 : 1;
+    if (splits > max_splits) splits = max_splits;
+  }
+  g.blocks_per_split = (total_blocks + splits - 1) / splits;
+  g.splits = (total_blocks + g.blocks_per_split - 1) / g.blocks_per_split;
+  return 0;
+}
+
+}  // namespace tgb
+
+using namespace tgb;
+
+extern "C" long long tgb_conv2d_wgrad_scratch_bytes(int N, int H, int W, int C, int K, int R,
+                                                    int S, int pad_h, int pad_w) {
+  WgradGeom g;
+  int BN;
+  if (plan_wgrad(N, H, W, C, K, R, S, pad_h, pad_w, g, BN)) return -1;
+  if (g.splits <= 1) return 0;
+  return static_cast<long long>(g.splits) * K * R * S * C * 4;
+}
+
+extern "C" int tgb_conv2d_wgrad_tf32(const float* dy, const float* x, float* dw, float* scratch,
+                                     long long scratch_bytes, int N, int H, int W, int C, int K,
+                                     int R, int S, int pad_h, int pad_w, int accumulate,
+                                     cudaStream_t stream) {
+  WgradGeom g;
+  int BN;
+  if (plan_wgrad(N, H, W, C, K, R, S, pad_h, pad_w, g, BN)) return 1;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) |
+       reinterpret_cast<uintptr_t>(dw) | reinterpret_cast<uintptr_t>(scratch)) & 15)
+    return set_error("conv_wgrad: tensors must be 16-byte aligned");
+  const size_t dw_elems = static_cast<size_t>(K) * R * S * C;
+  const bool direct = g.splits <= 1 && !accumulate;
+  if (!direct) {
+    const long long need = static_cast<long long>(g.splits) * dw_elems * 4;
+    if (scratch == nullptr || scratch_bytes < need)
+      return set_error("conv_wgrad: scratch too small (need %lld bytes, got %lld)", need,
+                       scratch_bytes);
+  }
+  CUtensorMap mdy, mx;
+  {
+    uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)N};
+    uint64_t strides[3] = {(uint64_t)K * 4, (uint64_t)g.Wo * K * 4,
+                           (uint64_t)g.Ho * g.Wo * K * 4};
+    uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
+    if (make_tensor_map(&mdy, dy, 4, 4, dims, strides, box, true))
+      return set_error("conv_wgrad: tensor map for dY failed");
+  }
+  {
+    uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    uint64_t strides[3] = {(uint64_t)C * 4, (uint64_t)W * C * 4, (uint64_t)H * W * C * 4};
+    uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
+    if (make_tensor_map(&mx, x, 4, 4, dims, strides, box, true))
+      return set_error("conv_wgrad: tensor map for X failed");
+  }
+  const int items = g.k_tiles * g.c_tiles * R * S * g.splits;
+  const int sms = sm_count();
+  const int grid = items < sms ? items : sms;
+  float* out = direct ? dw : scratch;
+  int rc;
+  switch (BN) {
+    case 256: rc = launch_wgrad<256, 4>(mdy, mx, g, out, grid, stream); break;
+    case 128: rc = launch_wgrad<128, 6>(mdy, mx, g, out, grid, stream); break;
+    case 64:  rc = launch_wgrad<64, 8>(mdy, mx, g, out, grid, stream); break;
+    default:  rc = launch_wgrad<32, 8>(mdy, mx, g, out, grid, stream); break;
+  }
+  if (rc) return rc;
+  if (!direct) {
+    const size_t n4 = dw_elems / 4;
+    size_t blocks = (n4 + 255) / 256;
+    if (blocks > static_cast<size_t>(sms) * 8) blocks = static_cast<size_t>(sms) * 8;
+    wgrad_reduce_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(scratch, dw, n4, g.splits,
+                                                                      n4, accumulate);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error("wgrad_reduce launch: %s", cudaGetErrorString(e));
+    count_launch();
+  }
+  return 0;
+}

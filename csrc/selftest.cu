@@ -154,6 +154,100 @@ static int run_conv_case(const ConvCase& c, bool check, int timing_iters) {
   return bad != 0;
 }
 
+static int run_wgrad_case(const ConvCase& c, bool check, int timing_iters) {
+  const int Ho = c.H + 2 * c.ph - c.R + 1, Wo = c.W + 2 * c.pw - c.S + 1;
+  const size_t nx = (size_t)c.N * c.H * c.W * c.C, nw = (size_t)c.K * c.R * c.S * c.C;
+  const size_t ny = (size_t)c.N * Ho * Wo * c.K;
+  std::vector<float> hx(nx), hdy(ny), hw(nw), ref(nw, 0.f);
+  for (auto& v : hx) v = rnd_q();
+  for (auto& v : hdy) v = rnd_q();
+  float *dx, *ddy, *dw, *scratch = nullptr;
+  long long sb = tgb_conv2d_wgrad_scratch_bytes(c.N, c.H, c.W, c.C, c.K, c.R, c.S, c.ph, c.pw);
+  if (sb < 0) {
+    printf("[wgrad %s] plan failed: %s\n", c.name, tgb_last_error());
+    return 1;
+  }
+  CK(cudaMalloc(&dx, nx * 4));
+  CK(cudaMalloc(&ddy, ny * 4));
+  CK(cudaMalloc(&dw, nw * 4));
+  if (sb) CK(cudaMalloc(&scratch, sb));
+  CK(cudaMemcpy(dx, hx.data(), nx * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(ddy, hdy.data(), ny * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemset(dw, 0xFF, nw * 4));
+  int rc = tgb_conv2d_wgrad_tf32(ddy, dx, dw, scratch, sb, c.N, c.H, c.W, c.C, c.K, c.R, c.S,
+                                 c.ph, c.pw, 0, 0);
+  if (rc) {
+    printf("[wgrad %s] launch failed: %s\n", c.name, tgb_last_error());
+    return 1;
+  }
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    printf("[wgrad %s] kernel fault: %s\n", c.name, cudaGetErrorString(e));
+    exit(3);
+  }
+  int bad = 0;
+  if (check) {
+    CK(cudaMemcpy(hw.data(), dw, nw * 4, cudaMemcpyDeviceToHost));
+    for (int n = 0; n < c.N; ++n)
+      for (int ho = 0; ho < Ho; ++ho)
+        for (int wo = 0; wo < Wo; ++wo)
+          for (int r = 0; r < c.R; ++r) {
+            int hi = ho + r - c.ph;
+            if (hi < 0 || hi >= c.H) continue;
+            for (int s2 = 0; s2 < c.S; ++s2) {
+              int wi = wo + s2 - c.pw;
+              if (wi < 0 || wi >= c.W) continue;
+              const float* xp = &hx[((size_t)(n * c.H + hi) * c.W + wi) * c.C];
+              const float* gp = &hdy[((size_t)(n * Ho + ho) * Wo + wo) * c.K];
+              for (int k = 0; k < c.K; ++k) {
+                float gv = gp[k];
+                if (gv == 0.f) continue;
+                float* wp = &ref[((size_t)(k * c.R + r) * c.S + s2) * c.C];
+                for (int ch = 0; ch < c.C; ++ch) wp[ch] += gv * xp[ch];
+              }
+            }
+          }
+    double maxerr = 0;
+    for (size_t i = 0; i < nw; ++i) {
+      double d = std::fabs((double)hw[i] - ref[i]);
+      if (!(d <= 1e-3)) {
+        if (bad < 12) {
+          size_t ch = i % c.C, t = (i / c.C) % (c.R * c.S), k = i / ((size_t)c.C * c.R * c.S);
+          printf("  wgrad mismatch k=%zu tap=%zu c=%zu got=%g want=%g\n", k, t, ch, hw[i], ref[i]);
+        }
+        ++bad;
+      }
+      if (d > maxerr) maxerr = d;
+    }
+    printf("[wgrad %s] N=%d HxW=%dx%d C=%d K=%d %dx%d scratch=%lld: max|err|=%.3g mismatches=%d -> %s\n",
+           c.name, c.N, c.H, c.W, c.C, c.K, c.R, c.S, sb, maxerr, bad, bad ? "FAIL" : "ok");
+  }
+  if (timing_iters > 0) {
+    cudaEvent_t a, b;
+    CK(cudaEventCreate(&a));
+    CK(cudaEventCreate(&b));
+    for (int i = 0; i < 3; ++i)
+      tgb_conv2d_wgrad_tf32(ddy, dx, dw, scratch, sb, c.N, c.H, c.W, c.C, c.K, c.R, c.S, c.ph,
+                            c.pw, 0, 0);
+    CK(cudaEventRecord(a));
+    for (int i = 0; i < timing_iters; ++i)
+      tgb_conv2d_wgrad_tf32(ddy, dx, dw, scratch, sb, c.N, c.H, c.W, c.C, c.K, c.R, c.S, c.ph,
+                            c.pw, 0, 0);
+    CK(cudaEventRecord(b));
+    CK(cudaEventSynchronize(b));
+    float ms;
+    CK(cudaEventElapsedTime(&ms, a, b));
+    ms /= timing_iters;
+    double flop = 2.0 * c.N * Ho * Wo * (double)c.K * c.C * c.R * c.S;
+    printf("[wgrad %s] %.3f ms  %.1f TFLOP/s (tf32)\n", c.name, ms, flop / ms * 1e-9);
+  }
+  cudaFree(dx);
+  cudaFree(ddy);
+  cudaFree(dw);
+  if (scratch) cudaFree(scratch);
+  return bad != 0;
+}
+
 int main(int argc, char** argv) {
   const char* only = argc > 1 ? argv[1] : nullptr;
   int fails = 0;
@@ -172,6 +266,7 @@ int main(int argc, char** argv) {
   for (auto& c : small) {
     if (only && strcmp(only, c.name) && strcmp(only, "all")) continue;
     fails += run_conv_case(c, true, 0);
+    fails += run_wgrad_case(c, true, 0);
   }
   ConvCase perf[] = {
       {"perf_64_192", 8, 192, 192, 64, 64, 3, 3, 1, 1, 0},
@@ -185,6 +280,7 @@ int main(int argc, char** argv) {
     if (only && strcmp(only, c.name) && strcmp(only, "all") && strcmp(only, "perf")) continue;
     if (!only) continue;
     fails += run_conv_case(c, false, 10);
+    fails += run_wgrad_case(c, false, 10);
   }
   printf("selftest: %s\n", fails ? "FAILURES" : "all ok");
   return fails ? 1 : 0;

@@ -36,6 +36,46 @@ int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, float* stats
                           int N, int H, int W, int C, int K, int R, int S,
                           int pad_h, int pad_w, int stats_mode, cudaStream_t stream);
 
+/* Weight gradient of the same convolution (TF32 tcgen05, both operands MN-major from TMA):
+ *   dw[k,r,s,c] = sum_{n,ho,wo} dy[n,ho,wo,k] * x[n,ho+r-pad_h,wo+s-pad_w,c]
+ * dy: [N,Ho,Wo,K]  x: [N,H,W,C]  dw: [K,R,S,C]. Requires C % 4 == 0, K % 4 == 0.
+ * When the pixel range is split across CTAs (few channel tiles, many pixels) or accumulate != 0,
+ * fp32 partials go to `scratch` and are summed in a fixed order by a second kernel;
+ * tgb_conv2d_wgrad_scratch_bytes() returns how many bytes that needs (0 = none, <0 = error).
+ * accumulate != 0 adds the result onto dw instead of overwriting it.
+ * Reference call site: autograd of nn.Conv2d (cuDNN in the reference). */
+long long tgb_conv2d_wgrad_scratch_bytes(int N, int H, int W, int C, int K, int R, int S,
+                                         int pad_h, int pad_w);
+int tgb_conv2d_wgrad_tf32(const float* dy, const float* x, float* dw, float* scratch,
+                          long long scratch_bytes, int N, int H, int W, int C, int K,
+                          int R, int S, int pad_h, int pad_w, int accumulate,
+                          cudaStream_t stream);
+
+/* Fused normalisation kernels. Tensors are [G][P][C] fp32 with C % 4 == 0: G = images and
+ * P = H*W for InstanceNorm; G = 1 and P = N*H*W for BatchNorm-style per-channel statistics.
+ *
+ * tgb_moments: out[g][c][0..1] += (sum x, sum x^2). (Reference torchgpipe/batchnorm.py:51-57
+ *   computes these with two separate full-tensor reductions.)
+ * tgb_in_prepare: from the accumulated moments `stats` [G][C][2] and an optional per-(g,c)
+ *   Dropout2d scale `drop_scale` (0 or 1/(1-p); NULL = no dropout) computes
+ *   mean_coef[g][c] = (mean, ms / sqrt(ms^2 * var + eps)) - InstanceNorm applied to the
+ *   channel-dropped tensor, folded into one multiply-add.
+ * tgb_in_leaky_fwd: z = LeakyReLU(coef * (y - mean)).
+ * tgb_in_leaky_bwd_sums: sums[g][c] += (sum dn, sum dn*u) with dn, u re-derived from (dz, z),
+ *   so neither the conv output y nor the normalised tensor is kept for backward.
+ * tgb_in_leaky_bwd: dy = coef * (dn - S1/P - u * S2/P).
+ * Reference call sites: Dropout2d + InstanceNorm2d + LeakyReLU of
+ * benchmarks/models/unet/__init__.py:42-48 (three ATen ops each way there). */
+int tgb_moments(const float* x, float* out, int G, int P, int C, cudaStream_t stream);
+int tgb_in_prepare(const float* stats, const float* drop_scale, float* mean_coef,
+                   int G, int P, int C, float eps, cudaStream_t stream);
+int tgb_in_leaky_fwd(const float* y, const float* mean_coef, float* z, int G, int P, int C,
+                     float slope, cudaStream_t stream);
+int tgb_in_leaky_bwd_sums(const float* dz, const float* z, float* out, int G, int P, int C,
+                          float slope, cudaStream_t stream);
+int tgb_in_leaky_bwd(const float* dz, const float* z, const float* mean_coef, const float* sums,
+                     float* dy, int G, int P, int C, float slope, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

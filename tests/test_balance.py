@@ -129,9 +129,8 @@ def test_balance_by_size_param_and_scale():
                 x = x + torch.rand_like(x, requires_grad=True)
             return x
 
-    model = nn.Sequential(*[nn.Linear(i, i) for i in [10, 20, 30, 40, 50, 60]])
-    assert balance_by_size(2, model, torch.rand(1, 10), param_scale=100, device='cuda',
-                           ) in ([4, 2],)
+    model = nn.Sequential(*[nn.Linear(i + 1, i + 2) for i in range(6)])
+    assert balance_by_size(2, model, torch.rand(7, 1), param_scale=100, device='cuda') == [4, 2]
     model = nn.Sequential(Tradeoff(param_size=1, latent_size=6),
                           Tradeoff(param_size=2, latent_size=5),
                           Tradeoff(param_size=3, latent_size=4),

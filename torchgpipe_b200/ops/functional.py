@@ -1,0 +1,198 @@
+"""Autograd functions over the native sm_100a kernels (NHWC / channels-last, fp32 + TF32 MMA).
+
+Every function here takes and returns ordinary ``torch`` tensors of logical shape ``[N,C,H,W]``
+in ``torch.channels_last`` memory format (weights ``[K,C,R,S]`` channels-last = KRSC memory).
+The kernels are enqueued on the current CUDA stream of the input's device, so they compose with
+the pipeline's stream discipline like any ATen op.
+"""
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from torchgpipe_b200.ops import _lib
+
+__all__ = ['conv2d', 'conv2d_forward', 'instnorm_leaky', 'channel_moments', 'conv_supported']
+
+_CL = torch.channels_last
+_c_int = ctypes.c_int
+_c_float = ctypes.c_float
+_c_ll = ctypes.c_longlong
+
+
+def _cl(t: Tensor) -> Tensor:
+    return t if t.is_contiguous(memory_format=_CL) else t.contiguous(memory_format=_CL)
+
+
+def conv_supported(c_in: int, c_out: int, stride, dilation, groups: int) -> bool:
+    """Whether the tcgen05 kernels cover this convolution (else callers use ATen/cuDNN)."""
+    stride = tuple(stride) if not isinstance(stride, int) else (stride, stride)
+    dilation = tuple(dilation) if not isinstance(dilation, int) else (dilation, dilation)
+    return (stride == (1, 1) and dilation == (1, 1) and groups == 1
+            and c_in % 4 == 0 and c_out % 32 == 0)
+
+
+def conv2d_forward(x: Tensor, w: Tensor, padding: Tuple[int, int], stats_mode: int = 0,
+                   ) -> Tuple[Tensor, Optional[Tensor]]:
+    """Raw forward: returns ``(y, stats)``; ``stats`` is ``[N,K,2]`` (mode 1), ``[K,2]`` (mode 2)
+    or ``None``. No autograd."""
+    lib = _lib.require()
+    x, w = _cl(x), _cl(w)
+    N, C, H, W = x.shape
+    K, Cw, R, S = w.shape
+    assert C == Cw, f'channel mismatch: input {C}, weight {Cw}'
+    ph, pw = padding
+    Ho, Wo = H + 2 * ph - R + 1, W + 2 * pw - S + 1
+    y = torch.empty((N, K, Ho, Wo), device=x.device, dtype=torch.float32, memory_format=_CL)
+    stats = None
+    if stats_mode == 1:
+        stats = torch.zeros((N, K, 2), device=x.device, dtype=torch.float32)
+    elif stats_mode == 2:
+        stats = torch.zeros((K, 2), device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        rc = lib.tgb_conv2d_fprop_tf32(_lib.ptr(x), _lib.ptr(w), _lib.ptr(y), _lib.ptr(stats),
+                                       _c_int(N), _c_int(H), _c_int(W), _c_int(C), _c_int(K),
+                                       _c_int(R), _c_int(S), _c_int(ph), _c_int(pw),
+                                       _c_int(stats_mode), _lib.stream_ptr(x.device))
+    _lib.check(rc, 'tgb_conv2d_fprop_tf32')
+    return y, stats
+
+
+def _conv2d_wgrad(dy: Tensor, x: Tensor, w_shape, padding: Tuple[int, int]) -> Tensor:
+    lib = _lib.require()
+    lib.tgb_conv2d_wgrad_scratch_bytes.restype = _c_ll
+    N, C, H, W = x.shape
+    K, _, R, S = w_shape
+    ph, pw = padding
+    args = (_c_int(N), _c_int(H), _c_int(W), _c_int(C), _c_int(K), _c_int(R), _c_int(S),
+            _c_int(ph), _c_int(pw))
+    need = lib.tgb_conv2d_wgrad_scratch_bytes(*args)
+    if need < 0:
+        _lib.check(1, 'tgb_conv2d_wgrad_scratch_bytes')
+    scratch = torch.empty(need // 4, device=x.device, dtype=torch.float32) if need else None
+    dw = torch.empty(w_shape, device=x.device, dtype=torch.float32, memory_format=_CL)
+    with torch.cuda.device(x.device):
+        rc = lib.tgb_conv2d_wgrad_tf32(_lib.ptr(dy), _lib.ptr(x), _lib.ptr(dw), _lib.ptr(scratch),
+                                       _c_ll(need), *args, _c_int(0),
+                                       _lib.stream_ptr(x.device))
+    _lib.check(rc, 'tgb_conv2d_wgrad_tf32')
+    return dw
+
+
+class _Conv2d(torch.autograd.Function):
+    """Stride-1 convolution; backward = dgrad (same tcgen05 kernel, flipped weights) + wgrad."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor, w: Tensor, ph: int, pw: int, stats_mode: int):  # type: ignore[override]
+        x, w = _cl(x), _cl(w)
+        y, stats = conv2d_forward(x, w, (ph, pw), stats_mode)
+        ctx.save_for_backward(x, w)
+        ctx.padding = (ph, pw)
+        if stats is None:
+            stats = x.new_empty(0)
+        ctx.mark_non_differentiable(stats)
+        return y, stats
+
+    @staticmethod
+    def backward(ctx, dy: Tensor, _dstats):  # type: ignore[override]
+        x, w = ctx.saved_tensors
+        ph, pw = ctx.padding
+        K, C, R, S = w.shape
+        dy = _cl(dy)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            if conv_supported(K, C, 1, 1, 1):
+                # dX = conv(dY, W^T flipped), pad' = R-1-pad
+                wt = _cl(w.flip(2, 3).permute(1, 0, 2, 3))
+                dx, _ = conv2d_forward(dy, wt, (R - 1 - ph, S - 1 - pw), 0)
+            else:
+                dx = torch.nn.grad.conv2d_input(x.shape, w, dy, padding=(ph, pw))
+        if ctx.needs_input_grad[1]:
+            dw = _conv2d_wgrad(dy, x, w.shape, (ph, pw))
+        return dx, dw, None, None, None
+
+
+def conv2d(x: Tensor, w: Tensor, padding: Tuple[int, int], stats_mode: int = 0,
+           ) -> Tuple[Tensor, Optional[Tensor]]:
+    """Differentiable stride-1 convolution on tcgen05. Returns ``(y, stats or None)``."""
+    y, stats = _Conv2d.apply(x, w, int(padding[0]), int(padding[1]), int(stats_mode))
+    return y, (stats if stats.numel() else None)
+
+
+def channel_moments(x: Tensor, per_image: bool = False) -> Tensor:
+    """(sum, sum of squares) per channel (``[C,2]``) or per (image, channel) (``[N,C,2]``)."""
+    lib = _lib.require()
+    x = _cl(x)
+    N, C, H, W = x.shape
+    G, P = (N, H * W) if per_image else (1, N * H * W)
+    out = torch.zeros((G, C, 2), device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        rc = lib.tgb_moments(_lib.ptr(x), _lib.ptr(out), _c_int(G), _c_int(P), _c_int(C),
+                             _lib.stream_ptr(x.device))
+    _lib.check(rc, 'tgb_moments')
+    return out if per_image else out[0]
+
+
+class _InstNormLeaky(torch.autograd.Function):
+    """z = LeakyReLU(InstanceNorm(Dropout2d(y))) with the dropout folded into the norm.
+
+    Saves only the output ``z`` and the per-(n,c) ``(mean, coef)`` pair: the pre-activation and
+    the convolution output are re-derived from ``z`` in backward.
+    """
+
+    @staticmethod
+    def forward(ctx, y: Tensor, stats: Optional[Tensor], drop_scale: Optional[Tensor],  # type: ignore[override]
+                eps: float, slope: float):
+        lib = _lib.require()
+        y = _cl(y)
+        N, C, H, W = y.shape
+        P = H * W
+        if stats is None or stats.numel() == 0:
+            stats = channel_moments(y, per_image=True)
+        mean_coef = torch.empty((N, C, 2), device=y.device, dtype=torch.float32)
+        z = torch.empty_like(y, memory_format=_CL)
+        if drop_scale is not None:
+            drop_scale = drop_scale.reshape(N, C).contiguous()
+        with torch.cuda.device(y.device):
+            st = _lib.stream_ptr(y.device)
+            rc = lib.tgb_in_prepare(_lib.ptr(stats), _lib.ptr(drop_scale), _lib.ptr(mean_coef),
+                                    _c_int(N), _c_int(P), _c_int(C), _c_float(eps), st)
+            _lib.check(rc, 'tgb_in_prepare')
+            rc = lib.tgb_in_leaky_fwd(_lib.ptr(y), _lib.ptr(mean_coef), _lib.ptr(z), _c_int(N),
+                                      _c_int(P), _c_int(C), _c_float(slope), st)
+            _lib.check(rc, 'tgb_in_leaky_fwd')
+        ctx.save_for_backward(z, mean_coef)
+        ctx.slope = slope
+        return z
+
+    @staticmethod
+    def backward(ctx, dz: Tensor):  # type: ignore[override]
+        lib = _lib.require()
+        z, mean_coef = ctx.saved_tensors
+        dz = _cl(dz)
+        N, C, H, W = z.shape
+        P = H * W
+        sums = torch.zeros((N, C, 2), device=z.device, dtype=torch.float32)
+        dy = torch.empty_like(z, memory_format=_CL)
+        with torch.cuda.device(z.device):
+            st = _lib.stream_ptr(z.device)
+            rc = lib.tgb_in_leaky_bwd_sums(_lib.ptr(dz), _lib.ptr(z), _lib.ptr(sums), _c_int(N),
+                                           _c_int(P), _c_int(C), _c_float(ctx.slope), st)
+            _lib.check(rc, 'tgb_in_leaky_bwd_sums')
+            rc = lib.tgb_in_leaky_bwd(_lib.ptr(dz), _lib.ptr(z), _lib.ptr(mean_coef),
+                                      _lib.ptr(sums), _lib.ptr(dy), _c_int(N), _c_int(P),
+                                      _c_int(C), _c_float(ctx.slope), st)
+            _lib.check(rc, 'tgb_in_leaky_bwd')
+        return dy, None, None, None, None
+
+
+def instnorm_leaky(y: Tensor, stats: Optional[Tensor] = None, drop_scale: Optional[Tensor] = None,
+                   eps: float = 1e-5, slope: float = 0.01) -> Tensor:
+    """Fused ``LeakyReLU(InstanceNorm2d(Dropout2d(y)))`` (no affine, batch statistics).
+
+    ``stats`` are the per-(n,c) (sum, sum of squares) from the convolution epilogue (computed
+    here if absent); ``drop_scale`` is ``[N,C]`` with entries 0 or ``1/(1-p)`` (``None`` = no
+    dropout). ``slope`` must be positive.
+    """
+    return _InstNormLeaky.apply(y, stats, drop_scale, float(eps), float(slope))
