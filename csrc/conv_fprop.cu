@@ -53,7 +53,8 @@ struct SmemLayout {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kEpiBytes = kBlockM * kBlockKBytes;     // 16 KB per staging buffer
   static constexpr int kEpiOffset = STAGES * kStageBytes;
-  static constexpr int kBarOffset = kEpiOffset + 2 * kEpiBytes;
+  static constexpr int kStatOffset = kEpiOffset + 2 * kEpiBytes;   // 1 KB partials + 512 B table
+  static constexpr int kBarOffset = kStatOffset + 1536;
   static constexpr int kTotal = kBarOffset + (2 * STAGES + 4) * 8 + 16;
 };
 
@@ -190,12 +191,30 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
     const int row = q * 32 + lane;                // tile row owned by this thread
     const int epi_tid = threadIdx.x - 128;
     uint8_t* epi = smem + L::kEpiOffset;
+    float2* stat_part = reinterpret_cast<float2*>(smem + L::kStatOffset);     // [4 warps][32]
+    int* row_img = reinterpret_cast<int*>(smem + L::kStatOffset + 1024);      // [128]
     int acc = 0;
     uint32_t acc_phase = 0;
     int chunk_counter = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int kt, tw, th, tn;
       decode_tile(tile, kt, tw, th, tn);
+      bool tile_uniform = false;
+      if (g.stats_mode != 0) {
+        tile_uniform = g.BNB == 1 && (tw + 1) * g.BW <= g.Wo && (th + 1) * g.BH <= g.Ho;
+        if (!tile_uniform) {
+          // image index of every tile row (or -1 when the row is outside the output); the
+          // table is published by the first bar.sync of the chunk loop. The barrier keeps a
+          // fast warp from overwriting the table a slower warp still reads for the last tile.
+          asm volatile("bar.sync 2, 128;" ::: "memory");
+          const int ww = row % g.BW;
+          const int hh = (row / g.BW) % g.BH;
+          const int nn = row / (g.BW * g.BH);
+          const bool inside = row < rows_valid && tw * g.BW + ww < g.Wo &&
+                              th * g.BH + hh < g.Ho && tn * g.BNB + nn < g.N;
+          row_img[row] = inside ? (g.stats_mode == 1 ? tn * g.BNB + nn : 0) : -1;
+        }
+      }
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
 #pragma unroll 1
@@ -234,43 +253,61 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
           tma_store_commit();
         }
         if (g.stats_mode != 0) {
-          // column sums over this warp's 32 rows, read back from the staging buffer:
-          // lane = column, so each LDS hits 32 distinct words of one 128B row (no conflicts)
+          // Column sums over this warp's 32 rows, read back from the staging buffer:
+          // lane = column, so each LDS hits 32 distinct words of one 128B row (no conflicts).
           const int col = lane;
           const int kglob = kt * BN + j * kEpiChunk + col;
-          const int pix_per_img = g.BW * g.BH;
-          float s1 = 0.f, s2 = 0.f;
-          int cur_img = -1;
-          for (int rr = 0; rr < 32; ++rr) {
-            const int r2 = q * 32 + rr;
-            if (r2 >= rows_valid) break;
-            // rows of a partial tile that fall outside the output contribute nothing
-            const int ww = r2 % g.BW;
-            const int hh = (r2 / g.BW) % g.BH;
-            const int nn = r2 / pix_per_img;
-            if (tw * g.BW + ww >= g.Wo || th * g.BH + hh >= g.Ho || tn * g.BNB + nn >= g.N)
-              continue;
-            const int img = (g.stats_mode == 1) ? (tn * g.BNB + nn) : 0;
-            if (img != cur_img) {
-              if (cur_img >= 0 && cur_img < g.N && kglob < g.K) {
-                float* dst = stats + (static_cast<size_t>(cur_img) * g.K + kglob) * 2;
-                atomicAdd(dst, s1);
-                atomicAdd(dst + 1, s2);
-              }
-              cur_img = img;
-              s1 = 0.f;
-              s2 = 0.f;
+          const int sw_hi = col >> 2, sw_lo = (col & 3) * 4;
+          if (tile_uniform) {
+            // whole tile inside one image and inside the output: no per-row bookkeeping
+            float s1 = 0.f, s2 = 0.f;
+            const int r_end = min(32, rows_valid - q * 32);
+#pragma unroll 8
+            for (int rr = 0; rr < r_end; ++rr) {
+              const int r2 = q * 32 + rr;
+              const float x = *reinterpret_cast<const float*>(
+                  buf + r2 * kBlockKBytes + ((sw_hi ^ (r2 & 7)) << 4) + sw_lo);
+              s1 += x;
+              s2 = fmaf(x, x, s2);
             }
-            const int pc = (col >> 2) ^ (r2 & 7);
-            const float x = *reinterpret_cast<const float*>(buf + r2 * kBlockKBytes + pc * 16 +
-                                                            (col & 3) * 4);
-            s1 += x;
-            s2 = fmaf(x, x, s2);
-          }
-          if (cur_img >= 0 && cur_img < g.N && kglob < g.K) {
-            float* dst = stats + (static_cast<size_t>(cur_img) * g.K + kglob) * 2;
-            atomicAdd(dst, s1);
-            atomicAdd(dst + 1, s2);
+            stat_part[q * 32 + col] = make_float2(s1, s2);
+            asm volatile("bar.sync 2, 128;" ::: "memory");
+            if (q == 0 && kglob < g.K) {
+              const float2 p0 = stat_part[col], p1 = stat_part[32 + col];
+              const float2 p2 = stat_part[64 + col], p3 = stat_part[96 + col];
+              const int img = (g.stats_mode == 1) ? tn : 0;
+              float* dst = stats + (static_cast<size_t>(img) * g.K + kglob) * 2;
+              atomicAdd(dst, (p0.x + p1.x) + (p2.x + p3.x));
+              atomicAdd(dst + 1, (p0.y + p1.y) + (p2.y + p3.y));
+            }
+          } else {
+            float s1 = 0.f, s2 = 0.f;
+            int cur_img = -1;
+            for (int rr = 0; rr < 32; ++rr) {
+              const int r2 = q * 32 + rr;
+              if (r2 >= rows_valid) break;
+              const int img = row_img[r2];          // -1: row lies outside the output
+              if (img < 0) continue;
+              if (img != cur_img) {
+                if (cur_img >= 0 && kglob < g.K) {
+                  float* dst = stats + (static_cast<size_t>(cur_img) * g.K + kglob) * 2;
+                  atomicAdd(dst, s1);
+                  atomicAdd(dst + 1, s2);
+                }
+                cur_img = img;
+                s1 = 0.f;
+                s2 = 0.f;
+              }
+              const float x = *reinterpret_cast<const float*>(
+                  buf + r2 * kBlockKBytes + ((sw_hi ^ (r2 & 7)) << 4) + sw_lo);
+              s1 += x;
+              s2 = fmaf(x, x, s2);
+            }
+            if (cur_img >= 0 && kglob < g.K) {
+              float* dst = stats + (static_cast<size_t>(cur_img) * g.K + kglob) * 2;
+              atomicAdd(dst, s1);
+              atomicAdd(dst + 1, s2);
+            }
           }
         }
       }
@@ -370,7 +407,7 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
     uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
     uint64_t strides[3] = {(uint64_t)C * 4, (uint64_t)W * C * 4, (uint64_t)H * W * C * 4};
     uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
-    if (make_tensor_map(&mx, x, 4, 4, dims, strides, box, true))
+    if (make_tensor_map(&mx, x, 4, 4, dims, strides, box, 1))
       return set_error("conv_fprop: tensor map for X failed");
   }
   {
@@ -379,7 +416,7 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
     uint64_t dims[4] = {(uint64_t)C, (uint64_t)(R * S), (uint64_t)K, 1};
     uint64_t strides[3] = {(uint64_t)C * 4, (uint64_t)R * S * C * 4, (uint64_t)K * R * S * C * 4};
     uint32_t box[4] = {32, 1, (uint32_t)BN, 1};
-    if (make_tensor_map(&mw, w, 4, 4, dims, strides, box, true))
+    if (make_tensor_map(&mw, w, 4, 4, dims, strides, box, 1))
       return set_error("conv_fprop: tensor map for W failed");
   }
   {
@@ -387,7 +424,7 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
     uint64_t strides[3] = {(uint64_t)K * 4, (uint64_t)g.Wo * K * 4,
                            (uint64_t)g.Ho * g.Wo * K * 4};
     uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
-    if (make_tensor_map(&my, y, 4, 4, dims, strides, box, true))
+    if (make_tensor_map(&my, y, 4, 4, dims, strides, box, 1))
       return set_error("conv_fprop: tensor map for Y failed");
   }
   const int sms = sm_count();

@@ -5,9 +5,11 @@
 // GEMM view per filter tap: M = K (output channels), N = C (input channels), and the reduction
 // runs over all N*Ho*Wo output pixels. In NHWC memory the reduction index is the *outer*
 // dimension of both operands, so both are fed to the tensor core as MN-major (transposed)
-// operands straight from the TMA boxes: a box of P pixels x 32 channels with the 128-byte
-// swizzle IS the canonical MN-major SWIZZLE_128B layout ((4,8,m),(8,k)):((1,4,LBO),(32,SBO))
-// (fp32 elements), with one MMA (K=8) consuming one 8-pixel swizzle atom of every channel chunk.
+// operands straight from the TMA boxes. For 32-bit MN-major operands tcgen05 accepts exactly one
+// shared-memory layout, SWIZZLE_128B_BASE32B: 128-byte rows (32 channels of one pixel) whose four
+// 32-byte atoms are XOR-ed with (pixel % 4); TMA writes that layout with
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, so a box of P pixels x 32 channels lands ready to use and
+// one MMA (K = 8 pixels) consumes two 4-pixel swizzle atoms of every channel chunk.
 // The X box is shifted by the tap offset and zero-filled outside the image by TMA (= padding).
 //
 // Work item = (k-tile of 128, c-tile of BN, tap, split of the pixel range); persistent CTAs.
@@ -20,6 +22,7 @@
 #include "sm100_ptx.cuh"
 #include "tensormap.h"
 #include "tgb_internal.h"
+#include <cstdlib>
 
 namespace tgb {
 
@@ -36,6 +39,8 @@ struct WgradGeom {
   int tiles_w, tiles_h, tiles_n;         // pixel blocks
   int k_tiles, c_tiles, splits;
   int blocks_per_split;
+  int desc_lbo, desc_sbo, desc_layout;   // shared-memory descriptor fields (bytes, bytes, type)
+  int dbg_shift, dbg_ksteps, dbg_baseoff; // bring-up probes (0 = off), see plan_wgrad
 };
 
 template <int BN, int STAGES>
@@ -142,7 +147,9 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmap_dy,
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      const int k_steps = g.P / 8;
+      const int k_steps = g.dbg_ksteps > 0 ? g.dbg_ksteps : g.P / 8;
+      const uint64_t dbg_add = static_cast<uint64_t>(g.dbg_shift * 8) |
+                               (static_cast<uint64_t>(g.dbg_baseoff & 7) << 49);
       for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
         int kt, ct, tap, split;
         decode(item, kt, ct, tap, split);
@@ -157,12 +164,14 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmap_dy,
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
           const uint32_t b_addr = a_addr + L::kABytes;
-          // MN-major SW128: LBO = stride between 32-channel chunks, SBO = between 8-pixel atoms
-          const uint64_t a_desc = make_smem_desc_sw128(a_addr, kWgChunkBytes, 1024);
-          const uint64_t b_desc = make_smem_desc_sw128(b_addr, kWgChunkBytes, 1024);
+          // MN-major, 128B swizzle with 32-byte atoms: LBO = stride between 32-channel chunks,
+          // SBO = stride between 4-pixel swizzle atoms (512 B)
+          const uint64_t a_desc = make_smem_desc(a_addr, g.desc_lbo, g.desc_sbo, g.desc_layout);
+          const uint64_t b_desc = make_smem_desc(b_addr, g.desc_lbo, g.desc_sbo, g.desc_layout);
           for (int k = 0; k < k_steps; ++k) {
             // next 8 pixels = next 1024-byte swizzle atom: +64 in the (addr >> 4) field
-            mma_tf32_ss(d_tmem, a_desc + 64 * k, b_desc + 64 * k, idesc, first ? 0u : 1u);
+            mma_tf32_ss(d_tmem, a_desc + 64 * k + dbg_add, b_desc + 64 * k + dbg_add, idesc,
+                        first ? 0u : 1u);
             first = false;
           }
           mma_commit(&empty_bar[stage]);
@@ -275,6 +284,14 @@ static void choose_wgrad_box(int N, int Ho, int Wo, int& BW, int& BH, int& BNB) 
     }
 }
 
+static int wgrad_tma_swizzle() {
+  if (const char* env = getenv("TGB_WGRAD_DESC")) {
+    int a, b, c, d;
+    if (sscanf(env, "%d,%d,%d,%d", &a, &b, &c, &d) == 4) return d;
+  }
+  return 2;
+}
+
 template <int BN, int STAGES>
 static int launch_wgrad(const CUtensorMap& mdy, const CUtensorMap& mx, const WgradGeom& g,
                         float* out, int grid, cudaStream_t stream) {
@@ -327,6 +344,25 @@ static int plan_wgrad(int N, int H, int W, int C, int K, int R, int S, int pad_h
   }
   g.blocks_per_split = (total_blocks + splits - 1) / splits;
   g.splits = (total_blocks + g.blocks_per_split - 1) / g.blocks_per_split;
+  g.desc_lbo = kWgChunkBytes;
+  g.desc_sbo = 512;
+  g.desc_layout = kLayoutSw128Base32;
+  g.dbg_shift = g.dbg_ksteps = g.dbg_baseoff = 0;
+  // Bring-up probe: TGB_WGRAD_DBG="shift_rows,k_steps,base_offset" starts both operands
+  // `shift_rows` pixels into the box (does tcgen05 swizzle by absolute address?).
+  if (const char* env = getenv("TGB_WGRAD_DBG")) {
+    int a, b, c;
+    if (sscanf(env, "%d,%d,%d", &a, &b, &c) == 3) {
+      g.dbg_shift = a; g.dbg_ksteps = b; g.dbg_baseoff = c;
+    }
+  }
+  // Bring-up aid: TGB_WGRAD_DESC="lbo,sbo,layout,tma_swizzle" overrides the descriptor fields.
+  if (const char* env = getenv("TGB_WGRAD_DESC")) {
+    int a, b, c, d;
+    if (sscanf(env, "%d,%d,%d,%d", &a, &b, &c, &d) == 4) {
+      g.desc_lbo = a; g.desc_sbo = b; g.desc_layout = c;
+    }
+  }
   return 0;
 }
 
@@ -367,14 +403,14 @@ extern "C" int tgb_conv2d_wgrad_tf32(const float* dy, const float* x, float* dw,
     uint64_t strides[3] = {(uint64_t)K * 4, (uint64_t)g.Wo * K * 4,
                            (uint64_t)g.Ho * g.Wo * K * 4};
     uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
-    if (make_tensor_map(&mdy, dy, 4, 4, dims, strides, box, true))
+    if (make_tensor_map(&mdy, dy, 4, 4, dims, strides, box, wgrad_tma_swizzle()))
       return set_error("conv_wgrad: tensor map for dY failed");
   }
   {
     uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
     uint64_t strides[3] = {(uint64_t)C * 4, (uint64_t)W * C * 4, (uint64_t)H * W * C * 4};
     uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
-    if (make_tensor_map(&mx, x, 4, 4, dims, strides, box, true))
+    if (make_tensor_map(&mx, x, 4, 4, dims, strides, box, wgrad_tma_swizzle()))
       return set_error("conv_wgrad: tensor map for X failed");
   }
   const int items = g.k_tiles * g.c_tiles * R * S * g.splits;

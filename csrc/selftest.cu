@@ -132,20 +132,22 @@ static int run_conv_case(const ConvCase& c, bool check, int timing_iters) {
     cudaEvent_t a, b;
     CK(cudaEventCreate(&a));
     CK(cudaEventCreate(&b));
+    float* st = c.stats_mode ? dstats : nullptr;
     for (int i = 0; i < 3; ++i)
-      tgb_conv2d_fprop_tf32(dx, dw, dy, nullptr, c.N, c.H, c.W, c.C, c.K, c.R, c.S, c.ph, c.pw, 0,
-                            0);
+      tgb_conv2d_fprop_tf32(dx, dw, dy, st, c.N, c.H, c.W, c.C, c.K, c.R, c.S, c.ph, c.pw,
+                            c.stats_mode, 0);
     CK(cudaEventRecord(a));
     for (int i = 0; i < timing_iters; ++i)
-      tgb_conv2d_fprop_tf32(dx, dw, dy, nullptr, c.N, c.H, c.W, c.C, c.K, c.R, c.S, c.ph, c.pw, 0,
-                            0);
+      tgb_conv2d_fprop_tf32(dx, dw, dy, st, c.N, c.H, c.W, c.C, c.K, c.R, c.S, c.ph, c.pw,
+                            c.stats_mode, 0);
     CK(cudaEventRecord(b));
     CK(cudaEventSynchronize(b));
     float ms;
     CK(cudaEventElapsedTime(&ms, a, b));
     ms /= timing_iters;
     double flop = 2.0 * c.N * Ho * Wo * (double)c.K * c.C * c.R * c.S;
-    printf("[%s] %.3f ms  %.1f TFLOP/s (tf32)\n", c.name, ms, flop / ms * 1e-9);
+    printf("[%s stats=%d] %.3f ms  %.1f TFLOP/s (tf32)\n", c.name, c.stats_mode, ms,
+           flop / ms * 1e-9);
   }
   cudaFree(dx);
   cudaFree(dw);
@@ -251,6 +253,66 @@ static int run_wgrad_case(const ConvCase& c, bool check, int timing_iters) {
 int main(int argc, char** argv) {
   const char* only = argc > 1 ? argv[1] : nullptr;
   int fails = 0;
+  if (only && !strcmp(only, "shift_probe")) {
+    // Does the MMA read a swizzled tile correctly when its start address is moved by whole
+    // 128-byte rows? 1x1 conv on a single 32-pixel line; only pixels [shift, shift+8*ks) count.
+    const int W = 32, C = 32, K = 128;
+    std::vector<float> hx((size_t)W * C), hdy((size_t)W * K), hw((size_t)K * C);
+    for (auto& v : hx) v = rnd_q();
+    for (auto& v : hdy) v = rnd_q();
+    float *dx, *ddy, *dw;
+    CK(cudaMalloc(&dx, hx.size() * 4));
+    CK(cudaMalloc(&ddy, hdy.size() * 4));
+    CK(cudaMalloc(&dw, hw.size() * 4));
+    CK(cudaMemcpy(dx, hx.data(), hx.size() * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ddy, hdy.data(), hdy.size() * 4, cudaMemcpyHostToDevice));
+    for (int shift = 0; shift <= 5; ++shift)
+      for (int baseoff = 0; baseoff < 8; ++baseoff) {
+        if (baseoff != 0 && baseoff != (shift & 7) && baseoff != (shift & 3) &&
+            baseoff != ((8 - shift) & 7) && baseoff != ((4 - shift) & 3))
+          continue;
+        const int ks = 3;
+        char env[64];
+        snprintf(env, sizeof env, "%d,%d,%d", shift, ks, baseoff);
+        setenv("TGB_WGRAD_DBG", env, 1);
+        CK(cudaMemset(dw, 0xFF, hw.size() * 4));
+        if (tgb_conv2d_wgrad_tf32(ddy, dx, dw, nullptr, 0, 1, 1, W, C, K, 1, 1, 0, 0, 0, 0)) {
+          printf("launch failed: %s\n", tgb_last_error());
+          return 1;
+        }
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) {
+          printf("shift=%d baseoff=%d: fault %s\n", shift, baseoff, cudaGetErrorString(e));
+          return 3;
+        }
+        CK(cudaMemcpy(hw.data(), dw, hw.size() * 4, cudaMemcpyDeviceToHost));
+        int bad = 0;
+        for (int k = 0; k < K; ++k)
+          for (int c = 0; c < C; ++c) {
+            float ref = 0.f;
+            for (int p = shift; p < shift + 8 * ks; ++p) ref += hdy[(size_t)p * K + k] * hx[(size_t)p * C + c];
+            if (std::fabs(hw[(size_t)k * C + c] - ref) > 1e-3) ++bad;
+          }
+        printf("shift_probe shift=%d base_offset=%d -> %s (%d mismatches)\n", shift, baseoff,
+               bad ? "FAIL" : "ok", bad);
+      }
+    unsetenv("TGB_WGRAD_DBG");
+    return 0;
+  }
+  if (only && !strcmp(only, "wgrad_sweep")) {
+    // lbo, sbo, layout type, TMA swizzle mode
+    const char* variants[] = {"4096,512,1,2", "512,4096,1,2", "4096,1024,1,2", "1024,4096,1,2",
+                              "4096,256,1,2", "4096,512,2,1", "4096,1024,2,1", "1024,4096,2,1",
+                              "4096,512,1,1", "4096,1024,2,2"};
+    ConvCase cs[] = {{"sweep_k128c64", 1, 16, 16, 64, 128, 1, 1, 0, 0, 0},
+                     {"sweep_k32c32", 2, 8, 16, 32, 32, 1, 1, 0, 0, 0}};
+    for (auto v : variants) {
+      setenv("TGB_WGRAD_DESC", v, 1);
+      printf("== variant lbo,sbo,layout,tma = %s\n", v);
+      for (auto& c : cs) run_wgrad_case(c, true, 0);
+    }
+    return 0;
+  }
   ConvCase small[] = {
       {"gemm1x1", 2, 8, 16, 32, 32, 1, 1, 0, 0, 0},
       {"gemm1x1_k64c64", 1, 16, 16, 64, 64, 1, 1, 0, 0, 2},
@@ -281,6 +343,25 @@ int main(int argc, char** argv) {
     if (!only) continue;
     fails += run_conv_case(c, false, 10);
     fails += run_wgrad_case(c, false, 10);
+  }
+  if (only && (!strcmp(only, "unet") || !strncmp(only, "unet_", 5))) {
+    // every distinct 3x3 layer of U-Net (5,64) at the benchmark's micro-batch of 40
+    struct { int C, K, HW; } layers[] = {
+        {64, 64, 192}, {64, 128, 96}, {128, 128, 96}, {128, 256, 48}, {256, 256, 48},
+        {256, 512, 24}, {512, 512, 24}, {512, 1024, 12}, {1024, 1024, 12}, {1024, 2048, 6},
+        {2048, 2048, 6}, {2048, 1024, 6}, {2048, 512, 12}, {512, 512, 12}, {1024, 256, 24},
+        {256, 256, 24}, {512, 128, 48}, {128, 128, 48}, {256, 64, 96}, {64, 64, 96},
+        {128, 32, 192}, {32, 32, 192}};
+    for (auto& l : layers) {
+      char name[64];
+      snprintf(name, sizeof name, "unet_%d_%d_%d", l.C, l.K, l.HW);
+      if (strcmp(only, "unet") && strcmp(only, name)) continue;
+      ConvCase c{name, 40, l.HW, l.HW, l.C, l.K, 3, 3, 1, 1, 0};
+      run_conv_case(c, false, 5);
+      ConvCase cs{name, 40, l.HW, l.HW, l.C, l.K, 3, 3, 1, 1, 1};
+      run_conv_case(cs, false, 5);
+      run_wgrad_case(c, false, 5);
+    }
   }
   printf("selftest: %s\n", fails ? "FAILURES" : "all ok");
   return fails ? 1 : 0;

@@ -173,15 +173,22 @@ __device__ __forceinline__ void tmem_ld_wait() {
 //   SBO            bits [32,46)  (bytes >> 4)
 //   version = 1    bits [46,48)
 //   layout type    bits [61,64)  2 = SWIZZLE_128B
-__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes,
-                                                         uint32_t sbo_bytes) {
+//                                1 = SWIZZLE_128B_BASE32B (32-byte atoms; MN-major 32-bit data)
+constexpr uint32_t kLayoutSw128 = 2;
+constexpr uint32_t kLayoutSw128Base32 = 1;
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes,
+                                                   uint32_t sbo_bytes, uint32_t layout_type) {
   uint64_t d = 0;
   d |= static_cast<uint64_t>((smem_addr >> 4) & 0x3FFF);
   d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= 1ull << 46;
-  d |= 2ull << 61;
+  d |= static_cast<uint64_t>(layout_type) << 61;
   return d;
+}
+__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes,
+                                                         uint32_t sbo_bytes) {
+  return make_smem_desc(smem_addr, lbo_bytes, sbo_bytes, kLayoutSw128);
 }
 
 // Instruction descriptor for kind::tf32 / kind::f16 with FP32 accumulation.

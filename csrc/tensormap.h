@@ -29,10 +29,12 @@ inline EncodeTiledFn encode_tiled_fn() {
 }
 
 // rank-`rank` fp32 (or 2-byte) tensor, dims[0] innermost. strides_bytes[i] is the stride of
-// dim i+1 (dim 0 is contiguous). Returns 0 on success.
+// dim i+1 (dim 0 is contiguous). swizzle_mode: 0 none, 1 = 128B (16-byte atoms, for K-major
+// operands and the epilogue), 2 = 128B with 32-byte atoms (the only layout tcgen05 accepts for
+// MN-major 32-bit operands). Returns 0 on success.
 inline int make_tensor_map(CUtensorMap* map, const void* base, int elem_bytes, int rank,
                            const uint64_t* dims, const uint64_t* strides_bytes,
-                           const uint32_t* box, bool swizzle128) {
+                           const uint32_t* box, int swizzle_mode) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (fn == nullptr) return -1;
   cuuint64_t gdims[5];
@@ -49,7 +51,9 @@ inline int make_tensor_map(CUtensorMap* map, const void* base, int elem_bytes, i
       elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   CUresult r = fn(map, dt, static_cast<cuuint32_t>(rank), const_cast<void*>(base), gdims,
                   gstrides, gbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                  swizzle_mode == 1   ? CU_TENSOR_MAP_SWIZZLE_128B
+                  : swizzle_mode == 2 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                                      : CU_TENSOR_MAP_SWIZZLE_NONE,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     fprintf(stderr, "cuTensorMapEncodeTiled failed: %d (rank %d)\n", static_cast<int>(r), rank);
