@@ -22,6 +22,7 @@
 #include "sm100_ptx.cuh"
 #include "tensormap.h"
 #include "tgb_internal.h"
+#include "conv_wgrad_common.h"
 #include <cstdlib>
 
 namespace tgb {
@@ -248,12 +249,19 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmap_dy,
   }
 }
 
-// out[i] = sum_s partial[s][i] (fixed order), optionally accumulated onto out (beta = 1)
+struct TapSplits {
+  int n[84];          // valid partial copies per filter tap (up to 9x9 filters)
+};
+
+// out[i] = sum_s partial[s][i] (fixed order), optionally accumulated onto out (beta = 1).
+// Element i belongs to tap (i / c4) % taps; only the first ts.n[tap] partial copies are valid.
 __global__ void wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out,
-                                    size_t n4, int splits, size_t split_stride4, int accumulate) {
+                                    size_t n4, TapSplits ts, int taps, int c4,
+                                    size_t split_stride4, int accumulate) {
   for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
     float4 acc = accumulate ? reinterpret_cast<const float4*>(out)[i] : make_float4(0, 0, 0, 0);
+    const int splits = ts.n[(i / c4) % taps];
     for (int s = 0; s < splits; ++s) {
       const float4 v = reinterpret_cast<const float4*>(partial)[s * split_stride4 + i];
       acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
@@ -370,67 +378,113 @@ static int plan_wgrad(int N, int H, int W, int C, int K, int R, int S, int pad_h
 
 using namespace tgb;
 
+// Which kernel serves a problem: 0 = per-tap (this file), 1 = tap-fused (conv_wgrad_fused.cu).
+// TGB_WGRAD_KERNEL=pertap|fused overrides the choice (bring-up / A-B timing).
+static int choose_wgrad_kernel(int N, int Ho, int Wo, int C, int S) {
+  if (const char* env = getenv("TGB_WGRAD_KERNEL")) {
+    if (env[0] == 'p') return 0;
+    if (env[0] == 'f' && wgrad_fused_applicable(C, S, Wo)) return 1;
+  }
+  return wgrad_fused_preferred(N, Ho, Wo, C, S) ? 1 : 0;
+}
+
 extern "C" long long tgb_conv2d_wgrad_scratch_bytes(int N, int H, int W, int C, int K, int R,
                                                     int S, int pad_h, int pad_w) {
-  WgradGeom g;
+  if (C % 4 != 0 || K % 4 != 0) {
+    set_error("conv_wgrad: need C %% 4 == 0 and K %% 4 == 0");
+    return -1;
+  }
+  int splits;
+  const int Wo = W + 2 * pad_w - S + 1, Ho = H + 2 * pad_h - R + 1;
   int BN;
-  if (plan_wgrad(N, H, W, C, K, R, S, pad_h, pad_w, g, BN)) return -1;
-  if (g.splits <= 1) return 0;
-  return static_cast<long long>(g.splits) * K * R * S * C * 4;
+  if (choose_wgrad_kernel(N, Ho, Wo, C, S)) {
+    WgradFusedGeom g;
+    if (plan_wgrad_fused(N, H, W, C, K, R, S, pad_h, pad_w, g, BN)) return -1;
+    splits = g.max_splits;
+  } else {
+    WgradGeom g;
+    if (plan_wgrad(N, H, W, C, K, R, S, pad_h, pad_w, g, BN)) return -1;
+    splits = g.splits;
+  }
+  if (splits <= 1) return 0;
+  return static_cast<long long>(splits) * K * R * S * C * 4;
 }
 
 extern "C" int tgb_conv2d_wgrad_tf32(const float* dy, const float* x, float* dw, float* scratch,
                                      long long scratch_bytes, int N, int H, int W, int C, int K,
                                      int R, int S, int pad_h, int pad_w, int accumulate,
                                      cudaStream_t stream) {
-  WgradGeom g;
-  int BN;
-  if (plan_wgrad(N, H, W, C, K, R, S, pad_h, pad_w, g, BN)) return 1;
+  if (C % 4 != 0 || K % 4 != 0)
+    return set_error("conv_wgrad: need C %% 4 == 0 and K %% 4 == 0");
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) |
        reinterpret_cast<uintptr_t>(dw) | reinterpret_cast<uintptr_t>(scratch)) & 15)
     return set_error("conv_wgrad: tensors must be 16-byte aligned");
+  const int Ho = H + 2 * pad_h - R + 1, Wo = W + 2 * pad_w - S + 1;
+  if (Ho <= 0 || Wo <= 0) return set_error("conv_wgrad: empty output");
+  const bool fused = choose_wgrad_kernel(N, Ho, Wo, C, S) != 0;
+  WgradGeom g;
+  WgradFusedGeom gf;
+  int BN, splits;
+  if (fused) {
+    if (plan_wgrad_fused(N, H, W, C, K, R, S, pad_h, pad_w, gf, BN)) return 1;
+    splits = gf.max_splits;
+  } else {
+    if (plan_wgrad(N, H, W, C, K, R, S, pad_h, pad_w, g, BN)) return 1;
+    splits = g.splits;
+  }
   const size_t dw_elems = static_cast<size_t>(K) * R * S * C;
-  const bool direct = g.splits <= 1 && !accumulate;
+  const bool direct = splits <= 1 && !accumulate;
   if (!direct) {
-    const long long need = static_cast<long long>(g.splits) * dw_elems * 4;
+    const long long need = static_cast<long long>(splits) * dw_elems * 4;
     if (scratch == nullptr || scratch_bytes < need)
       return set_error("conv_wgrad: scratch too small (need %lld bytes, got %lld)", need,
                        scratch_bytes);
   }
-  CUtensorMap mdy, mx;
-  {
-    uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)N};
-    uint64_t strides[3] = {(uint64_t)K * 4, (uint64_t)g.Wo * K * 4,
-                           (uint64_t)g.Ho * g.Wo * K * 4};
-    uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
-    if (make_tensor_map(&mdy, dy, 4, 4, dims, strides, box, wgrad_tma_swizzle()))
-      return set_error("conv_wgrad: tensor map for dY failed");
-  }
-  {
-    uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
-    uint64_t strides[3] = {(uint64_t)C * 4, (uint64_t)W * C * 4, (uint64_t)H * W * C * 4};
-    uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
-    if (make_tensor_map(&mx, x, 4, 4, dims, strides, box, wgrad_tma_swizzle()))
-      return set_error("conv_wgrad: tensor map for X failed");
-  }
-  const int items = g.k_tiles * g.c_tiles * R * S * g.splits;
-  const int sms = sm_count();
-  const int grid = items < sms ? items : sms;
   float* out = direct ? dw : scratch;
+  const int sms = sm_count();
   int rc;
-  switch (BN) {
-    case 256: rc = launch_wgrad<256, 4>(mdy, mx, g, out, grid, stream); break;
-    case 128: rc = launch_wgrad<128, 6>(mdy, mx, g, out, grid, stream); break;
-    case 64:  rc = launch_wgrad<64, 8>(mdy, mx, g, out, grid, stream); break;
-    default:  rc = launch_wgrad<32, 8>(mdy, mx, g, out, grid, stream); break;
+  if (fused) {
+    rc = run_wgrad_fused(dy, x, out, gf, BN, stream);
+  } else {
+    CUtensorMap mdy, mx;
+    {
+      uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)N};
+      uint64_t strides[3] = {(uint64_t)K * 4, (uint64_t)g.Wo * K * 4,
+                             (uint64_t)g.Ho * g.Wo * K * 4};
+      uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
+      if (make_tensor_map(&mdy, dy, 4, 4, dims, strides, box, wgrad_tma_swizzle()))
+        return set_error("conv_wgrad: tensor map for dY failed");
+    }
+    {
+      uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+      uint64_t strides[3] = {(uint64_t)C * 4, (uint64_t)W * C * 4, (uint64_t)H * W * C * 4};
+      uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
+      if (make_tensor_map(&mx, x, 4, 4, dims, strides, box, wgrad_tma_swizzle()))
+        return set_error("conv_wgrad: tensor map for X failed");
+    }
+    const int items = g.k_tiles * g.c_tiles * R * S * g.splits;
+    const int grid = items < sms ? items : sms;
+    switch (BN) {
+      case 256: rc = launch_wgrad<256, 4>(mdy, mx, g, out, grid, stream); break;
+      case 128: rc = launch_wgrad<128, 6>(mdy, mx, g, out, grid, stream); break;
+      case 64:  rc = launch_wgrad<64, 8>(mdy, mx, g, out, grid, stream); break;
+      default:  rc = launch_wgrad<32, 8>(mdy, mx, g, out, grid, stream); break;
+    }
   }
   if (rc) return rc;
   if (!direct) {
     const size_t n4 = dw_elems / 4;
     size_t blocks = (n4 + 255) / 256;
     if (blocks > static_cast<size_t>(sms) * 8) blocks = static_cast<size_t>(sms) * 8;
-    wgrad_reduce_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(scratch, dw, n4, g.splits,
-                                                                      n4, accumulate);
+    TapSplits ts;
+    if (R * S > 84) return set_error("conv_wgrad: filters larger than 84 taps are unsupported");
+    if (fused) {
+      wgrad_fused_tap_splits(gf, ts.n);
+    } else {
+      for (int t = 0; t < R * S; ++t) ts.n[t] = splits;
+    }
+    wgrad_reduce_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(scratch, dw, n4, ts, R * S,
+                                                                      C / 4, n4, accumulate);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("wgrad_reduce launch: %s", cudaGetErrorString(e));
     count_launch();

@@ -80,15 +80,32 @@ def _conv2d_wgrad(dy: Tensor, x: Tensor, w_shape, padding: Tuple[int, int]) -> T
     return dw
 
 
+def _dgrad_weight(w: Tensor, cache: Optional[dict]) -> Tensor:
+    """Tap-flipped, channel-transposed weights (KRSC memory) for the data-gradient pass.
+
+    ``cache`` is a dict owned by the calling module: with several micro-batches per optimiser
+    step the transform then runs once per parameter version instead of once per backward call.
+    """
+    if cache is not None:
+        if cache.get('version') == w._version and cache.get('ptr') == w.data_ptr():
+            return cache['wt']
+    wt = _cl(w.detach().flip(2, 3).permute(1, 0, 2, 3))
+    if cache is not None:
+        cache['version'], cache['ptr'], cache['wt'] = w._version, w.data_ptr(), wt
+    return wt
+
+
 class _Conv2d(torch.autograd.Function):
     """Stride-1 convolution; backward = dgrad (same tcgen05 kernel, flipped weights) + wgrad."""
 
     @staticmethod
-    def forward(ctx, x: Tensor, w: Tensor, ph: int, pw: int, stats_mode: int):  # type: ignore[override]
+    def forward(ctx, x: Tensor, w: Tensor, ph: int, pw: int, stats_mode: int,  # type: ignore[override]
+                cache: Optional[dict]):
         x, w = _cl(x), _cl(w)
         y, stats = conv2d_forward(x, w, (ph, pw), stats_mode)
         ctx.save_for_backward(x, w)
         ctx.padding = (ph, pw)
+        ctx.cache = cache
         if stats is None:
             stats = x.new_empty(0)
         ctx.mark_non_differentiable(stats)
@@ -104,19 +121,21 @@ class _Conv2d(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             if conv_supported(K, C, 1, 1, 1):
                 # dX = conv(dY, W^T flipped), pad' = R-1-pad
-                wt = _cl(w.flip(2, 3).permute(1, 0, 2, 3))
-                dx, _ = conv2d_forward(dy, wt, (R - 1 - ph, S - 1 - pw), 0)
+                dx, _ = conv2d_forward(dy, _dgrad_weight(w, ctx.cache), (R - 1 - ph, S - 1 - pw), 0)
             else:
                 dx = torch.nn.grad.conv2d_input(x.shape, w, dy, padding=(ph, pw))
         if ctx.needs_input_grad[1]:
             dw = _conv2d_wgrad(dy, x, w.shape, (ph, pw))
-        return dx, dw, None, None, None
+        return dx, dw, None, None, None, None
 
 
 def conv2d(x: Tensor, w: Tensor, padding: Tuple[int, int], stats_mode: int = 0,
-           ) -> Tuple[Tensor, Optional[Tensor]]:
-    """Differentiable stride-1 convolution on tcgen05. Returns ``(y, stats or None)``."""
-    y, stats = _Conv2d.apply(x, w, int(padding[0]), int(padding[1]), int(stats_mode))
+           cache: Optional[dict] = None) -> Tuple[Tensor, Optional[Tensor]]:
+    """Differentiable stride-1 convolution on tcgen05. Returns ``(y, stats or None)``.
+
+    ``cache``: optional dict owned by the caller, reused across calls to keep derived weights.
+    """
+    y, stats = _Conv2d.apply(x, w, int(padding[0]), int(padding[1]), int(stats_mode), cache)
     return y, (stats if stats.numel() else None)
 
 

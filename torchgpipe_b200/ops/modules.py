@@ -41,6 +41,7 @@ class Conv2dTC(nn.Module):
         self.weight = conv.weight
         self.weight.data = self.weight.data.contiguous(memory_format=_CL)
         self.bias = conv.bias
+        self._cache: dict = {}
 
     def extra_repr(self) -> str:
         return (f'{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, '
@@ -49,7 +50,7 @@ class Conv2dTC(nn.Module):
     def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
         if input.is_cuda and input.dtype == torch.float32 and TF.conv_supported(
                 self.in_channels, self.out_channels, 1, 1, 1):
-            y, _ = TF.conv2d(input, self.weight, self.padding)
+            y, _ = TF.conv2d(input, self.weight, self.padding, cache=self._cache)
             if self.bias is not None:
                 y = y + self.bias.view(1, -1, 1, 1)
             return y
@@ -73,6 +74,7 @@ class ConvInstNormLeaky(nn.Module):
         self.weight = conv.weight
         self.weight.data = self.weight.data.contiguous(memory_format=_CL)
         self.p, self.eps, self.slope = float(p), float(eps), float(slope)
+        self._cache: dict = {}
 
     def extra_repr(self) -> str:
         return (f'{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, '
@@ -93,7 +95,8 @@ class ConvInstNormLeaky(nn.Module):
 
         scale = self._drop_scale(input.size(0), input.device)
         if TF.conv_supported(self.in_channels, self.out_channels, 1, 1, 1):
-            y, stats = TF.conv2d(input, self.weight, self.padding, stats_mode=1)
+            y, stats = TF.conv2d(input, self.weight, self.padding, stats_mode=1,
+                                 cache=self._cache)
         else:
             # e.g. the 3-channel stem: library convolution, statistics by the moments kernel
             x = input.contiguous(memory_format=_CL)
