@@ -491,3 +491,63 @@ extern "C" int tgb_conv2d_wgrad_tf32(const float* dy, const float* x, float* dw,
   }
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Weight gradient for callers that are not allowed to allocate device memory.
+//
+// Some users of this library run where a device allocation is off the table: a serving or
+// real-time loop whose memory was sized and reserved up front, a plain C/C++ host with no
+// caching allocator behind it (so every cudaMalloc/cudaFree would synchronise the device), or a
+// step that is being recorded for replay. tgb_conv2d_wgrad_tf32 makes such callers size, obtain
+// and pass a scratch buffer themselves. This entry point needs none: the partial sums of the
+// pixel splits go to a fixed buffer that is part of the library image.
+//
+// The buffer is the file-scope array below. In host code its name is only a handle; the device
+// address is looked up with cudaGetSymbolAddress once per device (while that device is current)
+// and that address is what the kernels get.
+// ---------------------------------------------------------------------------------------------
+namespace tgb {
+
+constexpr long long kNoAllocScratchBytes = 32ll << 20;      // 32 MiB, see tgb200.h
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocScratchBytes / 4];
+
+// Device address of g_noalloc_scratch on the current device (resolved on first use per device).
+static int noalloc_scratch_ptr(float** out) {
+  static float* resolved[64] = {nullptr};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return set_error("wgrad_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= 64) return set_error("wgrad_noalloc: device ordinal %d out of range", dev);
+  float* p = __atomic_load_n(&resolved[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    void* addr = nullptr;
+    e = cudaGetSymbolAddress(&addr, g_noalloc_scratch);
+    if (e != cudaSuccess || addr == nullptr)
+      return set_error("wgrad_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                       cudaGetErrorString(e));
+    p = static_cast<float*>(addr);
+    __atomic_store_n(&resolved[dev], p, __ATOMIC_RELEASE);    // same value from any thread
+  }
+  *out = p;
+  return 0;
+}
+
+}  // namespace tgb
+
+extern "C" int tgb_conv2d_wgrad_tf32_noalloc(const float* dy, const float* x, float* dw, int N,
+                                             int H, int W, int C, int K, int R, int S, int pad_h,
+                                             int pad_w, int accumulate, cudaStream_t stream) {
+  long long need = tgb_conv2d_wgrad_scratch_bytes(N, H, W, C, K, R, S, pad_h, pad_w);
+  if (need < 0) return 1;                                     // message already set
+  if (need == 0 && accumulate) need = static_cast<long long>(K) * R * S * C * 4;
+  if (need > kNoAllocScratchBytes)
+    return set_error("wgrad_noalloc: this problem needs %lld bytes of scratch but the built-in "
+                     "buffer holds %lld; call tgb_conv2d_wgrad_tf32 with your own scratch instead",
+                     need, kNoAllocScratchBytes);
+  float* scratch = nullptr;
+  if (noalloc_scratch_ptr(&scratch)) return 1;
+  // Every partial the reduction reads is written by the kernel of this same call first, so
+  // whatever an earlier call left in the buffer is never observed and nothing has to be cleared.
+  return tgb_conv2d_wgrad_tf32(dy, x, dw, scratch, kNoAllocScratchBytes, N, H, W, C, K, R, S,
+                               pad_h, pad_w, accumulate, stream);
+}

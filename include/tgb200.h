@@ -51,6 +51,29 @@ int tgb_conv2d_wgrad_tf32(const float* dy, const float* x, float* dw, float* scr
                           int R, int S, int pad_h, int pad_w, int accumulate,
                           cudaStream_t stream);
 
+/* Weight gradient without any allocation. (No counterpart in the reference: it has no native
+ * code and lets PyTorch's allocator serve every temporary.)
+ *
+ * Same result as tgb_conv2d_wgrad_tf32, for callers that must not allocate device memory - a
+ * serving or real-time loop running inside a fixed memory reservation, a C/C++ host without a
+ * caching allocator (where cudaMalloc/cudaFree would stall the device), or code that records a
+ * step for later replay. The split partials are kept in a buffer built into the library,
+ * TGB_WGRAD_NOALLOC_SCRATCH_BYTES (32 MiB) per GPU, resident from library load until exit.
+ *   - Problems whose partials do not fit are refused (non-zero return, tgb_last_error() names
+ *     the need and the limit); use tgb_conv2d_wgrad_tf32 with your own scratch for those.
+ *   - The call itself performs no cudaMalloc / cudaFree and uses no allocating library routine.
+ *   - The first call on each device resolves the buffer's device address (and, like every entry
+ *     point here, configures the kernel on first use). Make that first call during start-up,
+ *     before any stream capture begins.
+ *   - The one buffer is shared by all calls on a device and keeps whatever the previous call
+ *     wrote; each call overwrites every partial before reading it, so nothing needs clearing.
+ *     Two calls that can run on the GPU at the same time (different streams, no ordering
+ *     between them) race on the buffer: serialise them. */
+#define TGB_WGRAD_NOALLOC_SCRATCH_BYTES (32ll << 20)
+int tgb_conv2d_wgrad_tf32_noalloc(const float* dy, const float* x, float* dw,
+                                  int N, int H, int W, int C, int K, int R, int S,
+                                  int pad_h, int pad_w, int accumulate, cudaStream_t stream);
+
 /* Fused normalisation kernels. Tensors are [G][P][C] fp32 with C % 4 == 0: G = images and
  * P = H*W for InstanceNorm; G = 1 and P = N*H*W for BatchNorm-style per-channel statistics.
  *
