@@ -389,6 +389,12 @@ class DistributedGPipe:
         if grad is None:
             return torch.zeros_like(leaf)
         leaf.grad = None
+        if grad.stride() != leaf.stride():
+            # the peer allocates its receive buffer with the layout of the tensor it sent
+            # forward; ship the gradient in that same (dense) layout
+            fmt = torch.channels_last if (leaf.dim() == 4 and not leaf.is_contiguous()) \
+                else torch.contiguous_format
+            grad = grad.contiguous(memory_format=fmt)
         return grad
 
 

@@ -120,7 +120,9 @@ class ProcessGroupTransport(Transport):
             if t.dim() > _MAX_DIMS:
                 raise ValueError(f'at most {_MAX_DIMS} dims per tensor')
             dims = list(t.shape) + [0] * (_MAX_DIMS - t.dim())
-            header += [_DTYPES.index(t.dtype), t.dim()] + dims
+            cl = t.dim() == 4 and not t.is_contiguous() and \
+                t.is_contiguous(memory_format=torch.channels_last)
+            header += [_DTYPES.index(t.dtype) + (100 if cl else 0), t.dim()] + dims
         header += [0] * (_HEADER_LEN - len(header))
         return torch.tensor(header, dtype=torch.int64, device=self.device)
 
@@ -130,10 +132,10 @@ class ProcessGroupTransport(Transport):
         out = []
         pos = 2
         for _ in range(values[0]):
-            dtype = _DTYPES[values[pos]]
+            dtype = _DTYPES[values[pos] % 100]
             ndim = values[pos + 1]
             shape = tuple(values[pos + 2:pos + 2 + ndim])
-            out.append((dtype, shape))
+            out.append((dtype, shape, values[pos] >= 100))
             pos += 2 + _MAX_DIMS
         return bool(values[1]), out
 
@@ -148,13 +150,14 @@ class ProcessGroupTransport(Transport):
             # Gradient messages never need a header: the receiver passes `like`.
             self._pending.append(self.dist.isend(self._encode(tensors, atomic), peer, group=self.group))
             self._known_send[slot] = True
+        # Completed sends are dropped right away: a pending handle keeps its tensor alive, and
+        # activations are large (a leaked handle per message grows memory by GBs per step).
+        self._reap()
         for t in tensors:
             t = t.detach()
-            if not t.is_contiguous():
+            if not (t.is_contiguous() or t.is_contiguous(memory_format=torch.channels_last)):
                 t = t.contiguous()
             self._pending.append(self.dist.isend(t, peer, group=self.group))
-        if len(self._pending) > 4096:
-            self._reap()
 
     def recv(self, src: int, key: Key, like: Optional[TensorOrTensors] = None,
              ) -> TensorOrTensors:
@@ -162,7 +165,9 @@ class ProcessGroupTransport(Transport):
         slot = (src, key)
         if like is not None:
             atomic = torch.is_tensor(like)
-            meta = [(t.dtype, tuple(t.shape)) for t in ((like,) if atomic else like)]
+            meta = [(t.dtype, tuple(t.shape), t.dim() == 4 and not t.is_contiguous()
+                     and t.is_contiguous(memory_format=torch.channels_last))
+                    for t in ((like,) if atomic else like)]
         elif self.static_shapes and slot in self._known_recv:
             atomic, meta = self._known_recv[slot]
         else:
@@ -172,8 +177,10 @@ class ProcessGroupTransport(Transport):
             self._known_recv[slot] = (atomic, meta)
         out = []
         works = []
-        for dtype, shape in meta:
-            buf = torch.empty(shape, dtype=dtype, device=self.device)
+        for dtype, shape, channels_last in meta:
+            buf = torch.empty(shape, dtype=dtype, device=self.device,
+                              memory_format=torch.channels_last if channels_last
+                              else torch.contiguous_format)
             works.append(self.dist.irecv(buf, peer, group=self.group))
             out.append(buf)
         for w in works:
