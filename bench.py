@@ -207,7 +207,8 @@ def run_ours(args):
         workers = {r: f'stage{r}' for r in range(world)}
         tp = ProcessGroupTransport(device)
         pipe = DistributedGPipe(model, rank, workers, balance, chunks, device=device,
-                                checkpoint='except_last', transport=tp)
+                                checkpoint='except_last', transport=tp,
+                                cuda_graphs=not args.no_graphs)
         params = list(pipe.model().parameters())
         dev_input = host_input.to(device) if first else None
         target = torch.ones(batch, 1, INPUT_HW, INPUT_HW, device=device) if last else None
@@ -241,9 +242,14 @@ def run_ours(args):
     for _ in range(args.warmup):
         step()
         flush()
-    launches_before = ops.launch_count()
+    def total_launches():
+        replayed = pipe.native_launches_replayed() if hasattr(pipe, 'native_launches_replayed') \
+            else 0
+        return ops.launch_count() + replayed
+
+    launches_before = total_launches()
     ms, _ = timed_loop(torch, dist, lambda: step(), args.steps, 0, device, flush, world)
-    launches = ops.launch_count() - launches_before
+    launches = total_launches() - launches_before
     clocks = sampler.stop() if sampler else None
 
     # end to end: H2D of the step's input from pinned memory + D2H of the loss, every step
@@ -258,10 +264,20 @@ def run_ours(args):
 
     _, e2e_wall = timed_loop(torch, dist, e2e_step, args.steps, 1, device, flush, world)
 
+    pipeline_report = None
     if world > 1:
         t = torch.tensor([float(launches)], device=device, dtype=torch.float64)
         dist.all_reduce(t)
         launches = int(t.item())
+        # one extra (untimed) step with per-pass CUDA events: bubble and exposed communication
+        pipe.timeline = True
+        step()
+        mine = pipe.timeline_report()
+        pipe.timeline = False
+        gathered = [None] * world
+        dist.all_gather_object(gathered, mine)
+        pipeline_report = {'per_rank': [{k: round(v, 3) for k, v in (g or {}).items()}
+                                        for g in gathered]}
 
     samples = batch * args.steps
     value = samples / (ms / 1e3)
@@ -280,12 +296,14 @@ def run_ours(args):
                    'parallelism': 'pp%d' % n,
                    'transport': 'single-process' if world == 1 else 'nccl-p2p',
                    'l2': 'flushed between steps (256 MiB write)',
-                   'kernels': 'off' if args.no_kernels else 'sm100'},
+                   'kernels': 'off' if args.no_kernels else 'sm100',
+                   'cuda_graphs': bool(world > 1 and not args.no_graphs)},
         'clocks': clocks,
         'e2e': {'value': e2e_value, 'unit': 'samples/s',
                 'h2d_bytes_per_step': host_input.numel() * 4, 'd2h_bytes_per_step': 4,
                 'ms_per_step': e2e_wall / args.steps},
         'gpu_launches': launches,
+        'pipeline': pipeline_report,
     }
     if rank == 0:
         print(json.dumps(result), flush=True)
@@ -445,6 +463,8 @@ def main():
     p.add_argument('--warmup', type=int, default=3)
     p.add_argument('--impl', choices=['ours', 'reference'], default='ours')
     p.add_argument('--model', choices=['unet'], default='unet')
+    p.add_argument('--no-graphs', action='store_true',
+                   help='ours arm, N>1: issue stage kernels eagerly instead of replaying CUDA graphs')
     p.add_argument('--no-kernels', action='store_true',
                    help='ours arm: keep torch/cuDNN ops (diagnostic; not the product path)')
     args = p.parse_args()

@@ -344,6 +344,11 @@ int main(int argc, char** argv) {
     fails += run_conv_case(c, false, 10);
     fails += run_wgrad_case(c, false, 10);
   }
+  int unet_batch = 40;
+  if (only && !strncmp(only, "unetb", 5)) {     // "unetb16": the layer table at micro-batch 16
+    unet_batch = atoi(only + 5);
+    only = "unet";
+  }
   if (only && (!strcmp(only, "unet") || !strncmp(only, "unet_", 5))) {
     // every distinct 3x3 layer of U-Net (5,64) at the benchmark's micro-batch of 40
     struct { int C, K, HW; } layers[] = {
@@ -356,9 +361,9 @@ int main(int argc, char** argv) {
       char name[64];
       snprintf(name, sizeof name, "unet_%d_%d_%d", l.C, l.K, l.HW);
       if (strcmp(only, "unet") && strcmp(only, name)) continue;
-      ConvCase c{name, 40, l.HW, l.HW, l.C, l.K, 3, 3, 1, 1, 0};
+      ConvCase c{name, unet_batch, l.HW, l.HW, l.C, l.K, 3, 3, 1, 1, 0};
       run_conv_case(c, false, 5);
-      ConvCase cs{name, 40, l.HW, l.HW, l.C, l.K, 3, 3, 1, 1, 1};
+      ConvCase cs{name, unet_batch, l.HW, l.HW, l.C, l.K, 3, 3, 1, 1, 1};
       run_conv_case(cs, false, 5);
       run_wgrad_case(c, false, 5);
     }

@@ -92,7 +92,8 @@ class _StageSkipTracker(SkipTracker):
 class _Flight:
     """Everything a rank keeps about one micro-batch between forward and backward."""
 
-    __slots__ = ('leaves', 'n_boundary', 'outputs', 'n_outputs', 'atomic', 'atomic_in')
+    __slots__ = ('leaves', 'n_boundary', 'outputs', 'n_outputs', 'atomic', 'atomic_in', 'rng',
+                 'staged')
 
     def __init__(self) -> None:
         self.leaves: Tensors = ()
@@ -101,6 +102,8 @@ class _Flight:
         self.n_outputs = 0
         self.atomic = True
         self.atomic_in = True
+        self.rng = None
+        self.staged = None
 
 
 class DistributedGPipe:
@@ -120,6 +123,11 @@ class DistributedGPipe:
             or ``'always'``.
         transport: a :class:`Transport`; default is the in-process channel
             backend driven through ``_put``/``_get``.
+        cuda_graphs: replay each stage pass from CUDA graphs
+            (:class:`~torchgpipe_b200.runtime.graphs.GraphedStage`): one graph
+            launch per micro-batch instead of hundreds of kernel launches.
+            Implies checkpointing of every micro-batch while training; needs a
+            CUDA ``device``, static shapes per micro-batch and host-sync-free layers.
     """
 
     #: The number of micro-batches.
@@ -147,6 +155,7 @@ class DistributedGPipe:
                  deferred_batch_norm: bool = False,
                  checkpoint: str = 'never',
                  transport: Optional[Transport] = None,
+                 cuda_graphs: bool = False,
                  ) -> None:
         microbatch_chunks = int(microbatch_chunks)
         checkpoint = str(checkpoint)
@@ -202,6 +211,13 @@ class DistributedGPipe:
         self._outputs: List[Optional[TensorOrTensors]] = [None] * microbatch_chunks
         self._flights: List[Optional[_Flight]] = [None] * microbatch_chunks
         self._live = 0      # micro-batches produced by the latest forward()
+        self.cuda_graphs = bool(cuda_graphs) and device is not None and \
+            torch.device(device).type == 'cuda'
+        self._graphed: Dict[Tuple[int, bool], Any] = {}
+        #: set to True to record CUDA events around every stage pass (see timeline_report)
+        self.timeline = False
+        self._marks: List[Tuple[str, Any, Any, Any]] = []
+        self._bytes_received = 0
 
     # -- topology ----------------------------------------------------------------
     @property
@@ -217,6 +233,50 @@ class DistributedGPipe:
 
     def _next_worker(self) -> Optional[str]:
         return None if self.is_last else self.workers[self.rank + 1]
+
+    # -- per-pass timeline -------------------------------------------------------
+    def _mark(self) -> Any:
+        if not (self.timeline and self.device is not None
+                and torch.device(self.device).type == 'cuda'):
+            return None
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record(torch.cuda.current_stream(self.device))
+        return ev
+
+    def timeline_report(self, reset: bool = True) -> Dict[str, float]:
+        """Summary of the passes recorded since the last reset (synchronises the device).
+
+        ``busy_ms``: time the compute stream spent inside stage passes; ``recv_wait_ms``: time
+        it sat waiting for activations / gradients from the neighbours (pipeline bubble plus
+        any communication that was not overlapped); ``span_ms``: first pass start to last pass
+        end; ``bubble_frac`` = 1 - busy/span; ``comm_ms_bound``: bytes received over the
+        measured 770 GB/s peer bandwidth - an upper bound on the exposed communication, which
+        is also bounded by ``recv_wait_ms``.
+        """
+        if not self._marks:
+            return {}
+        torch.cuda.synchronize(self.device)
+        busy = sum(t1.elapsed_time(t2) for _, _, t1, t2 in self._marks)
+        wait = sum(t0.elapsed_time(t1) for _, t0, t1, _ in self._marks)
+        span = self._marks[0][1].elapsed_time(self._marks[-1][3])
+        comm_bound = self._bytes_received / 770e9 * 1e3
+        report = {'busy_ms': busy, 'recv_wait_ms': wait, 'span_ms': span,
+                  'bubble_frac': max(0.0, 1.0 - busy / span) if span > 0 else 0.0,
+                  'bytes_received': float(self._bytes_received), 'comm_ms_bound': comm_bound,
+                  'exposed_comm_ms_bound': min(wait, comm_bound)}
+        if reset:
+            self._marks = []
+            self._bytes_received = 0
+        return report
+
+    def _count_bytes(self, value: Any) -> None:
+        if self.timeline:
+            for t in ((value,) if torch.is_tensor(value) else value):
+                self._bytes_received += t.numel() * t.element_size()
+
+    def native_launches_replayed(self) -> int:
+        """Native-kernel launches issued through CUDA-graph replays so far (graph mode)."""
+        return sum(st.native_launches_replayed for st in self._graphed.values())
 
     def model(self) -> nn.Sequential:
         """This rank's stage (give its parameters to the local optimiser)."""
@@ -281,10 +341,12 @@ class DistributedGPipe:
 
         for mb in range(m):
             flight = _Flight()
+            t0 = self._mark()
             if pieces is not None:
                 received: TensorOrTensors = pieces[mb].value
             else:
                 received = tp.recv(self.rank - 1, ('fwd', mb, 0))
+                self._count_bytes(received)
             atomic_in = torch.is_tensor(received)
             moved = to(self.device, received)
             boundary = tuple(self._as_leaf(t, grad_mode and not self.is_first)
@@ -292,7 +354,9 @@ class DistributedGPipe:
             skips = []
             for slot, src, _ in self._routes_in:
                 t = tp.recv(src, ('skip', mb, slot))
+                self._count_bytes(t)
                 skips.append(self._as_leaf(to(self.device, t), grad_mode))
+            t1 = self._mark()
 
             leaves = boundary + tuple(skips)
             flight.leaves = leaves
@@ -300,7 +364,18 @@ class DistributedGPipe:
             flight.atomic_in = atomic_in
             function = self._stage_function(len(boundary), atomic_in, flight)
 
-            if mb < stop:
+            if self.cuda_graphs:
+                staged = self._graphed_stage(len(boundary), atomic_in, flight)
+                flight.staged = staged
+                produced, flight.rng = staged.forward(leaves)
+                flight.n_outputs, flight.atomic = staged.meta['n_outputs'], staged.meta['atomic']
+                if self.is_last and grad_mode:
+                    # the caller differentiates its loss w.r.t. these leaves; backward() feeds
+                    # their .grad to the backward graph
+                    for y in produced[:flight.n_outputs]:
+                        if y.is_floating_point():
+                            y.requires_grad_()
+            elif mb < stop:
                 chk = Checkpointing(function, Batch(leaves))
                 out_batch = chk.checkpoint()
                 chk.recompute(out_batch)
@@ -308,6 +383,8 @@ class DistributedGPipe:
             else:
                 produced = function(leaves)
 
+            if t0 is not None:
+                self._marks.append(('fwd', t0, t1, self._mark()))
             outs = produced[:flight.n_outputs]
             stashes = produced[flight.n_outputs:]
             flight.outputs = produced
@@ -339,6 +416,8 @@ class DistributedGPipe:
         tp = self.transport
         if losses is not None:
             assert self.is_last, 'only the last stage takes losses'
+        for staged in self._graphed.values():
+            staged.refresh_derived_weights()     # once per step, outside the graphs
 
         for mb in reversed(range(self._live)):
             flight = self._flights[mb]
@@ -346,6 +425,12 @@ class DistributedGPipe:
             produced = flight.outputs
             outs = produced[:flight.n_outputs]
             stashes = produced[flight.n_outputs:]
+
+            if flight.staged is not None:
+                self._graphed_backward(mb, flight, losses)
+                self._flights[mb] = None
+                self._outputs[mb] = None
+                continue
 
             roots: List[Tensor] = []
             grads: List[Optional[Tensor]] = []
@@ -382,6 +467,65 @@ class DistributedGPipe:
 
             self._flights[mb] = None
             self._outputs[mb] = None
+
+    def _graphed_stage(self, n_boundary: int, atomic_in: bool, flight: _Flight) -> Any:
+        key = (n_boundary, atomic_in)
+        staged = self._graphed.get(key)
+        if staged is None:
+            from torchgpipe_b200.runtime.graphs import GraphedStage
+            meta: Dict[str, Any] = {}
+            probe = _Flight()
+            inner = self._stage_function(n_boundary, atomic_in, probe)
+
+            def function(inputs: Tensors) -> Tensors:
+                out = inner(inputs)
+                meta['n_outputs'], meta['atomic'] = probe.n_outputs, probe.atomic
+                return out
+
+            staged = GraphedStage(function, self.module, torch.device(self.device))
+            staged.meta = meta
+            self._graphed[key] = staged
+        return staged
+
+    def _graphed_backward(self, mb: int, flight: _Flight, losses: Optional[List[Tensor]]) -> None:
+        tp = self.transport
+        produced = flight.outputs
+        outs = produced[:flight.n_outputs]
+        stashes = produced[flight.n_outputs:]
+        gouts: List[Optional[Tensor]] = []
+        t0 = self._mark()
+        if losses is not None:
+            if losses[mb].requires_grad:
+                losses[mb].backward()
+            gouts.extend(y.grad for y in outs)
+        else:
+            received = tp.recv(self.rank + 1, ('bwd', mb, 0),
+                               like=outs[0] if flight.atomic else outs)
+            self._count_bytes(received)
+            received = to(self.device, received)
+            gouts.extend((received,) if torch.is_tensor(received) else received)
+        for (slot, dst, _), t in zip(self._routes_out, stashes):
+            if not t.is_floating_point():
+                gouts.append(None)
+                continue
+            g = tp.recv(dst, ('skip_grad', mb, slot), like=t)
+            self._count_bytes(g)
+            gouts.append(to(self.device, g))
+        t1 = self._mark()
+
+        gin = flight.staged.backward(flight.leaves, flight.rng, gouts)
+        if t0 is not None:
+            self._marks.append(('bwd', t0, t1, self._mark()))
+
+        leaves = flight.leaves
+        nb = flight.n_boundary
+        if not self.is_first:
+            grads = tuple(torch.zeros_like(x) if g is None else g
+                          for x, g in zip(leaves[:nb], gin[:nb]))
+            tp.send(self.rank - 1, ('bwd', mb, 0), grads[0] if flight.atomic_in else grads)
+        for (slot, src, _), x, g in zip(self._routes_in, leaves[nb:], gin[nb:]):
+            if x.is_floating_point():
+                tp.send(src, ('skip_grad', mb, slot), torch.zeros_like(x) if g is None else g)
 
     @staticmethod
     def _grad_of(leaf: Tensor) -> Tensor:

@@ -13,7 +13,8 @@ from torch import Tensor
 
 from torchgpipe_b200.ops import _lib
 
-__all__ = ['conv2d', 'conv2d_forward', 'instnorm_leaky', 'channel_moments', 'conv_supported']
+__all__ = ['conv2d', 'conv2d_forward', 'instnorm_leaky', 'channel_moments', 'conv_supported',
+           'refresh_dgrad_weight']
 
 _CL = torch.channels_last
 _c_int = ctypes.c_int
@@ -91,8 +92,18 @@ def _dgrad_weight(w: Tensor, cache: Optional[dict]) -> Tensor:
             return cache['wt']
     wt = _cl(w.detach().flip(2, 3).permute(1, 0, 2, 3))
     if cache is not None:
+        old = cache.get('wt')
+        if old is not None and old.shape == wt.shape and old.device == wt.device:
+            old.copy_(wt)       # keep the address: captured CUDA graphs read this buffer
+            wt = old
         cache['version'], cache['ptr'], cache['wt'] = w._version, w.data_ptr(), wt
     return wt
+
+
+def refresh_dgrad_weight(w: Tensor, cache: dict) -> None:
+    """Brings a cached dgrad weight up to date in place (no-op if never built or current)."""
+    if 'wt' in cache and (cache.get('version') != w._version or cache.get('ptr') != w.data_ptr()):
+        _dgrad_weight(w, cache)
 
 
 class _Conv2d(torch.autograd.Function):

@@ -43,6 +43,10 @@ class Conv2dTC(nn.Module):
         self.bias = conv.bias
         self._cache: dict = {}
 
+    def refresh_derived_weights(self) -> None:
+        """Updates the cached dgrad weights in place after an optimiser step (CUDA-graph mode)."""
+        TF.refresh_dgrad_weight(self.weight, self._cache)
+
     def extra_repr(self) -> str:
         return (f'{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, '
                 f'padding={self.padding}, tcgen05/tf32')
@@ -80,6 +84,10 @@ class ConvInstNormLeaky(nn.Module):
         return (f'{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, '
                 f'padding={self.padding}, dropout2d={self.p}, eps={self.eps}, '
                 f'leaky={self.slope}, tcgen05/tf32')
+
+    def refresh_derived_weights(self) -> None:
+        """Updates the cached dgrad weights in place after an optimiser step (CUDA-graph mode)."""
+        TF.refresh_dgrad_weight(self.weight, self._cache)
 
     def _drop_scale(self, n: int, device: torch.device) -> Optional[Tensor]:
         if not self.training or self.p == 0.0:

@@ -1,0 +1,211 @@
+"""CUDA-graph replay of one pipeline stage (forward, and recompute + backward).
+
+Published GPipe configurations use tens to thousands of micro-batches per step
+(reference ``benchmarks/unet-speed/main.py:41-68``: 16-40; ResNet-101: up to
+1667). On a B200 a stage's kernels for one micro-batch take well under the time
+the host needs to issue them one by one, so an eager stage is launch-bound and
+extra GPUs buy nothing. ``GraphedStage`` records the kernels of one stage once
+per input signature and afterwards issues a whole stage pass with one
+``cudaGraphLaunch``:
+
+* ``forward(inputs)``  - copies the inputs into static buffers, replays the
+  forward graph and returns *copies* of the outputs (no autograd graph is kept:
+  the static activation buffers belong to the next replay);
+* ``backward(inputs, rng_state, grad_outputs)`` - restores the RNG state of that
+  forward, replays the forward graph again (this is GPipe's checkpoint
+  recomputation), replays the backward graph, adds the parameter gradients into
+  ``param.grad`` with one fused multi-tensor add and returns the input gradients.
+
+So a graphed stage always checkpoints every micro-batch: it keeps only the stage
+inputs between forward and backward, exactly the memory behaviour of
+``checkpoint='always'`` (reference ``torchgpipe/checkpoint.py``), and one set of
+static activations per stage instead of one per micro-batch.
+
+Everything the native kernels do on the host (tensor-map encoding, launch
+configuration) happens at capture time; derived weights (the tap-flipped dgrad
+weights) live in persistent buffers that are refreshed *outside* the graph once
+per optimiser step (``refresh_derived_weights``).
+"""
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+import torch
+from torch import Tensor, nn
+
+__all__ = ['GraphedStage']
+
+Signature = Tuple[Tuple[Tuple[int, ...], torch.dtype, bool, bool], ...]
+
+
+def _signature(inputs: Sequence[Tensor]) -> Signature:
+    return tuple((tuple(t.shape), t.dtype, t.requires_grad,
+                  t.dim() == 4 and not t.is_contiguous()) for t in inputs)
+
+
+class _Captured:
+    """Graphs and static buffers for one input signature."""
+
+    def __init__(self) -> None:
+        self.fwd = torch.cuda.CUDAGraph()
+        self.bwd: Optional[torch.cuda.CUDAGraph] = None
+        self.static_inputs: List[Tensor] = []
+        self.static_outputs: Tuple[Tensor, ...] = ()
+        self.static_grad_outputs: List[Optional[Tensor]] = []
+        self.static_grad_inputs: List[Optional[Tensor]] = []
+        self.static_grad_params: List[Optional[Tensor]] = []
+        self.native_launches_fwd = 0
+        self.native_launches_bwd = 0
+
+
+class GraphedStage:
+    """Replays ``function(tuple of tensors) -> tuple of tensors`` from CUDA graphs.
+
+    Args:
+        function: the stage as a pure tensor function (it may use parameters of
+            ``module``; it must not synchronise with the host).
+        module: owner of the parameters and buffers ``function`` uses.
+        device: CUDA device of the stage.
+        warmup: eager iterations on a side stream before capture.
+    """
+
+    def __init__(self, function: Callable[[Tuple[Tensor, ...]], Tuple[Tensor, ...]],
+                 module: nn.Module, device: torch.device, warmup: int = 2) -> None:
+        self.function = function
+        self.module = module
+        self.device = device
+        self.warmup = warmup
+        self.params = [p for p in module.parameters() if p.requires_grad]
+        self._captured: Dict[Signature, _Captured] = {}
+        self._pool = None
+        self._derived = [m for m in module.modules() if hasattr(m, 'refresh_derived_weights')]
+        self.replays = 0
+        self.native_launches_replayed = 0
+
+    # -- capture ---------------------------------------------------------------
+    def _capture(self, inputs: Sequence[Tensor]) -> _Captured:
+        from torchgpipe_b200 import ops
+        cap = _Captured()
+        with torch.cuda.device(self.device):
+            cap.static_inputs = [torch.empty_like(t).requires_grad_(t.requires_grad)
+                                 for t in inputs]
+            for s, t in zip(cap.static_inputs, inputs):
+                s.data.copy_(t)
+            diff_inputs = [s for s in cap.static_inputs if s.requires_grad]
+
+            def run_backward(outputs: Tuple[Tensor, ...], grad_outputs: List[Optional[Tensor]]):
+                pairs = [(o, g) for o, g in zip(outputs, grad_outputs) if g is not None]
+                if not pairs or not (diff_inputs or self.params):
+                    return ()
+                return torch.autograd.grad([o for o, _ in pairs], diff_inputs + self.params,
+                                           [g for _, g in pairs], allow_unused=True)
+
+            # Warm-up on a side stream: lazy initialisation (kernel attributes, caches, cuDNN
+            # plans) must not happen inside a capture.
+            side = torch.cuda.Stream(self.device)
+            side.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(side):
+                for _ in range(self.warmup):
+                    with torch.enable_grad():
+                        outs = self.function(tuple(cap.static_inputs))
+                    gouts = [torch.ones_like(o) if o.requires_grad else None for o in outs]
+                    run_backward(outs, gouts)
+                    del outs, gouts
+            torch.cuda.current_stream(self.device).wait_stream(side)
+            torch.cuda.synchronize(self.device)
+
+            if self._pool is None:
+                self._pool = torch.cuda.graph_pool_handle()
+
+            before = ops.launch_count()
+            with torch.cuda.graph(cap.fwd, pool=self._pool):
+                with torch.enable_grad():
+                    cap.static_outputs = tuple(self.function(tuple(cap.static_inputs)))
+            cap.native_launches_fwd = ops.launch_count() - before
+
+            cap.static_grad_outputs = [torch.zeros_like(o) if o.requires_grad else None
+                                       for o in cap.static_outputs]
+            if any(g is not None for g in cap.static_grad_outputs) and \
+                    (diff_inputs or self.params):
+                cap.bwd = torch.cuda.CUDAGraph()
+                before = ops.launch_count()
+                with torch.cuda.graph(cap.bwd, pool=self._pool):
+                    grads = run_backward(cap.static_outputs, cap.static_grad_outputs)
+                cap.native_launches_bwd = ops.launch_count() - before
+                n_in = len(diff_inputs)
+                it = iter(grads[:n_in])
+                cap.static_grad_inputs = [next(it) if s.requires_grad else None
+                                          for s in cap.static_inputs]
+                cap.static_grad_params = list(grads[n_in:])
+        return cap
+
+    def _get(self, inputs: Sequence[Tensor]) -> _Captured:
+        sig = _signature(inputs)
+        cap = self._captured.get(sig)
+        if cap is None:
+            cap = self._capture(inputs)
+            self._captured[sig] = cap
+        return cap
+
+    # -- replay ----------------------------------------------------------------
+    @staticmethod
+    def _load(static: Sequence[Tensor], values: Sequence[Tensor]) -> None:
+        for s, v in zip(static, values):
+            if s.data_ptr() != v.data_ptr():
+                s.data.copy_(v, non_blocking=True)
+
+    def forward(self, inputs: Sequence[Tensor]) -> Tuple[Tuple[Tensor, ...], Tensor]:
+        """Runs the stage without keeping activations.
+
+        Returns ``(fresh output tensors, rng_state)``; hand ``rng_state`` back to
+        :meth:`backward` so the recomputation draws the same random numbers. (The state is
+        taken here, after a possible first-use capture, which itself consumes random numbers.)
+        """
+        cap = self._get(inputs)
+        rng_state = torch.cuda.get_rng_state(self.device)
+        self._load(cap.static_inputs, inputs)
+        cap.fwd.replay()
+        self.replays += 1
+        self.native_launches_replayed += cap.native_launches_fwd
+        return tuple(o.detach().clone() for o in cap.static_outputs), rng_state
+
+    def refresh_derived_weights(self) -> None:
+        """Recomputes weights derived from parameters (call once per optimiser step)."""
+        for m in self._derived:
+            m.refresh_derived_weights()
+
+    def backward(self, inputs: Sequence[Tensor], rng_state: Optional[Tensor],
+                 grad_outputs: Sequence[Optional[Tensor]]) -> List[Optional[Tensor]]:
+        """Recomputes the stage for ``inputs`` and back-propagates ``grad_outputs``.
+
+        Parameter gradients are accumulated into ``param.grad``; the gradients of the inputs
+        that require grad are returned (``None`` for the others).
+        """
+        cap = self._get(inputs)
+        if cap.bwd is None:
+            return [None for _ in inputs]
+        if rng_state is not None:
+            torch.cuda.set_rng_state(rng_state, self.device)
+        self._load(cap.static_inputs, inputs)
+        cap.fwd.replay()                         # checkpoint recomputation
+        for s, g in zip(cap.static_grad_outputs, grad_outputs):
+            if s is not None:
+                if g is None:
+                    s.zero_()
+                else:
+                    s.copy_(g, non_blocking=True)
+        cap.bwd.replay()
+        self.replays += 2
+        self.native_launches_replayed += cap.native_launches_fwd + cap.native_launches_bwd
+
+        have, add_to, add_from = [], [], []
+        for p, g in zip(self.params, cap.static_grad_params):
+            if g is None:
+                continue
+            if p.grad is None:
+                p.grad = g.detach().clone()
+                have.append(p)
+            else:
+                add_to.append(p.grad)
+                add_from.append(g)
+        if add_to:
+            torch._foreach_add_(add_to, add_from)
+        return [None if g is None else g.detach().clone() for g in cap.static_grad_inputs]
