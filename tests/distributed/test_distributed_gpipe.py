@@ -249,9 +249,12 @@ def _gloo_worker(rank, world, port, balance, chunks, checkpoint, ret):
 
 
 @pytest.mark.timeout(180)
-@pytest.mark.parametrize('checkpoint', ['never', 'except_last'])
-def test_gloo_multiprocess_matches_plain_model(checkpoint):
-    world, balance, chunks = 2, [1, 3], 3
+@pytest.mark.parametrize('checkpoint,world,balance', [('never', 2, [1, 3]),
+                                                      ('except_last', 2, [1, 3]),
+                                                      ('except_last', 3, [1, 1, 2])])
+def test_gloo_multiprocess_matches_plain_model(checkpoint, world, balance):
+    # world 3 has a skip route 0 -> 2 that jumps over stage 1 (per-pair communicators)
+    chunks = 3
     port = 29500 + os.getpid() % 2000
     manager = mp.Manager()
     ret = manager.dict()
@@ -260,6 +263,6 @@ def test_gloo_multiprocess_matches_plain_model(checkpoint):
     model = _skip_model()
     x = torch.rand(6, 4, generator=torch.Generator().manual_seed(1))
     ref_grads, _ = _reference_grads(model, x, chunks)
-    got = ret[0] + ret[1]
+    got = sum((ret[r] for r in range(world)), [])
     for g, r in zip(got, ref_grads):
         assert torch.allclose(g, 2 * r, atol=1e-5)     # two accumulated steps

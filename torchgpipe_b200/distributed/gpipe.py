@@ -207,6 +207,10 @@ class DistributedGPipe:
         if transport is None:
             transport = ChannelTransport(workers, rank, type(self))
         self.transport = transport
+        # every pair of stages that will talk: neighbours, and the two ends of each skip route
+        pairs = [(r, r + 1) for r in range(len(workers) - 1)]
+        pairs += sorted({(src, dst) for _, src, dst, _ in routes})
+        transport.prepare_pairs(pairs)
 
         self._outputs: List[Optional[TensorOrTensors]] = [None] * microbatch_chunks
         self._flights: List[Optional[_Flight]] = [None] * microbatch_chunks
