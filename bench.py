@@ -168,7 +168,9 @@ def run_ours(args):
     device = torch.device('cuda', local_rank)
     torch.cuda.set_device(device)
     if world > 1:
-        dist.init_process_group('nccl', device_id=device)
+        # Lazy initialisation on purpose: point-to-point traffic then gets one NCCL communicator
+        # (and stream) per rank pair instead of being serialised through a single one.
+        dist.init_process_group('nccl')
     assert world in (1, n), f'launch with --nproc-per-node {n} (got WORLD_SIZE={world})'
 
     from torchgpipe_b200 import GPipe

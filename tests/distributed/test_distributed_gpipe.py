@@ -232,7 +232,7 @@ def _gloo_worker(rank, world, port, balance, chunks, checkpoint, ret):
         from torchgpipe_b200.distributed.transport import ProcessGroupTransport
         model = _skip_model()
         x = torch.rand(6, 4, generator=torch.Generator().manual_seed(1))
-        tp = ProcessGroupTransport(torch.device('cpu'))
+        tp = ProcessGroupTransport(torch.device('cpu'), pair_groups=True)
         pipe = DistributedGPipe(model, rank, {r: f'r{r}' for r in range(world)}, balance, chunks,
                                 device=torch.device('cpu'), checkpoint=checkpoint, transport=tp)
         for step in range(2):       # second step exercises the cached-shape path

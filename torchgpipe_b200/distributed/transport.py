@@ -99,7 +99,8 @@ class ProcessGroupTransport(Transport):
     """``torch.distributed`` point-to-point (NCCL on GPUs, gloo on CPU)."""
 
     def __init__(self, device: Optional[torch.device] = None, group: Any = None,
-                 ranks: Optional[Dict[int, int]] = None, static_shapes: bool = True) -> None:
+                 ranks: Optional[Dict[int, int]] = None, static_shapes: bool = True,
+                 pair_groups: bool = False) -> None:
         import torch.distributed as dist
         if not dist.is_initialized():
             raise RuntimeError('torch.distributed must be initialised before creating a '
@@ -110,6 +111,7 @@ class ProcessGroupTransport(Transport):
         self.ranks = ranks                  # stage rank -> global rank (identity by default)
         self.static_shapes = static_shapes
         self._pair_groups: Dict[Tuple[int, int], Any] = {}
+        self._use_pair_groups = pair_groups
         self._known_send: Dict[Tuple[int, Key], bool] = {}
         self._known_recv: Dict[Tuple[int, Key], Any] = {}
         self._pending: List[Any] = []
@@ -118,16 +120,22 @@ class ProcessGroupTransport(Transport):
         return stage_rank if self.ranks is None else self.ranks[stage_rank]
 
     def prepare_pairs(self, pairs: Sequence[Tuple[int, int]]) -> None:
-        """One communicator (and so one NCCL stream) per communicating pair of stages.
+        """One communicator (and so one stream) per communicating pair of stages.
 
         NCCL point-to-point is a rendezvous and all operations of one communicator run in
         issue order on one stream. With a single communicator, a skip tensor sent from stage 1
         to stage 6 parks stage 1's stream until stage 6 gets around to receiving it, and every
         later send of stage 1 - including the next micro-batch for stage 2 - queues behind it:
-        the pipeline degenerates to lock-step (measured: 8 stages slower than 4). Separate
-        communicators confine that ordering to each pair, where it is the natural order.
+        the pipeline degenerates to lock-step (measured: 8 stages slower than 4).
+
+        ``torch.distributed`` already gives every rank pair its own NCCL communicator for
+        point-to-point traffic when the process group is initialised *lazily* (no
+        ``device_id=`` in ``init_process_group``); eager initialisation funnels everything
+        through the one communicator. So the default here is to do nothing and to initialise
+        lazily (see ``bench.py``); ``pair_groups=True`` builds explicit two-rank groups instead
+        (used with gloo in the tests; with eagerly initialised NCCL it hung on 4 GPUs).
         """
-        if self.dist.get_world_size(self.group) <= 2:
+        if not self._use_pair_groups or self.dist.get_world_size(self.group) <= 2:
             return
         me = self.dist.get_rank()
         for a, b in pairs:
