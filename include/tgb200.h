@@ -99,6 +99,27 @@ int tgb_in_leaky_bwd_sums(const float* dz, const float* z, float* out, int G, in
 int tgb_in_leaky_bwd(const float* dz, const float* z, const float* mean_coef, const float* sums,
                      float* dy, int G, int P, int C, float slope, cudaStream_t stream);
 
+/* Fused gradient all-reduce across data-parallel replicas: out = scale * sum over replicas, in
+ * place in every replica's fp32 bucket, optionally also as a local bf16 copy. One kernel per
+ * rank: barrier, reduce-scatter (P2P loads from the peers' buckets, or multimem.ld_reduce through
+ * the NVSwitch when `multicast` is given), scale, all-gather (peer loads / multimem.st), barrier.
+ *   bufs, pads : host arrays of `world` device pointers - every replica's bucket and signal pad
+ *                as mapped on the calling GPU (symmetric memory); pads are zero-initialised
+ *                uint32 arrays of tgb_allreduce_pad_bytes(max_blocks) bytes used only by this call
+ *   n          : fp32 elements, multiple of 4*world
+ *   launch_index : same on every rank, +1 per call on these buffers (derives barrier tickets)
+ *   error_flag : device int set to 1 if a peer did not arrive within timeout_ms
+ * All replicas must launch the call; it must not be wrapped with other kernels that wait on a
+ * peer. Wire bytes per direction per GPU: P2P 2N(R-1)/R, multicast about 2N/R.
+ * Reference: none - the reference has no data parallelism; NCCL all_reduce on the
+ * same bucket is the baseline. */
+int tgb_allreduce_scale_f32(void* const* bufs, void* const* pads, void* multicast,
+                            void* cast_out_bf16, unsigned long long n, float scale,
+                            int rank, int world, unsigned int launch_index,
+                            int timeout_ms, int* error_flag, int max_blocks,
+                            cudaStream_t stream);
+unsigned long long tgb_allreduce_pad_bytes(int max_blocks);
+
 #ifdef __cplusplus
 }
 #endif
