@@ -201,6 +201,134 @@ in_backward_kernel(const float* __restrict__ dz, const float* __restrict__ z,
   }
 }
 
+// ------------------------------------------------------------------ BatchNorm (training)
+// From per-channel (sum, sum of squares) over P elements: coef[c] = (a, b) with
+// y_norm = y * a + b, a = gamma * rstd, b = beta - mean * a; saved[c] = (mean, rstd) for backward.
+// Optionally folds the batch statistics into the running estimates exactly like nn.BatchNorm2d
+// (unbiased variance for running_var, momentum < 0 selects the cumulative average 1/count).
+__global__ void bn_prepare_kernel(const float* __restrict__ stats, const float* __restrict__ gamma,
+                                  const float* __restrict__ beta, float* __restrict__ coef,
+                                  float* __restrict__ saved, float* __restrict__ running_mean,
+                                  float* __restrict__ running_var, int C, float inv_p,
+                                  float unbias, float eps, float momentum) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float mu = stats[2 * c] * inv_p;
+  const float var = fmaxf(stats[2 * c + 1] * inv_p - mu * mu, 0.f);
+  const float rstd = rsqrtf(var + eps);
+  const float g = gamma ? gamma[c] : 1.f;
+  const float a = g * rstd;
+  coef[2 * c] = a;
+  coef[2 * c + 1] = (beta ? beta[c] : 0.f) - mu * a;
+  saved[2 * c] = mu;
+  saved[2 * c + 1] = rstd;
+  if (running_mean != nullptr) {
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mu;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * var * unbias;
+  }
+}
+
+// z = act(y * a + b), act = ReLU or identity
+__global__ void __launch_bounds__(kEwThreads)
+bn_apply_kernel(const float* __restrict__ y, const float* __restrict__ coef,
+                float* __restrict__ z, size_t n4, int C, int relu) {
+  const int Q = C >> 2;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int q = static_cast<int>(i % Q);
+    const float4 c01 = ld4(coef + q * 8), c23 = ld4(coef + q * 8 + 4);
+    float4 v = ld4(y + i * 4);
+    v.x = fmaf(v.x, c01.x, c01.y); v.y = fmaf(v.y, c01.z, c01.w);
+    v.z = fmaf(v.z, c23.x, c23.y); v.w = fmaf(v.w, c23.z, c23.w);
+    if (relu) {
+      v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
+    }
+    st4(z + i * 4, v);
+  }
+}
+
+// sums[c] += (sum dn, sum dn * xhat); dn = dz masked by the ReLU (re-derived from y), xhat from y
+__global__ void __launch_bounds__(kEwThreads)
+bn_bwd_reduce_kernel(const float* __restrict__ dz, const float* __restrict__ y,
+                     const float* __restrict__ coef, const float* __restrict__ saved,
+                     float* __restrict__ sums, int P, int C, int slabs, int relu) {
+  const int Q = C >> 2;
+  const int pix_per_slab = (P + slabs - 1) / slabs;
+  const int p_begin = blockIdx.x * pix_per_slab;
+  const int p_end = min(P, p_begin + pix_per_slab);
+  extern __shared__ float sh[];
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  const size_t n4 = static_cast<size_t>(max(p_end - p_begin, 0)) * Q;
+  // channel quad of a thread is fixed when Q divides the block size: accumulate in registers
+  const bool fixed = (kEwThreads % Q) == 0;
+  float4 a1 = make_float4(0, 0, 0, 0), a2 = make_float4(0, 0, 0, 0);
+  for (size_t i = threadIdx.x; i < n4; i += blockDim.x) {
+    const int q = static_cast<int>(i % Q);
+    const size_t off = (static_cast<size_t>(p_begin) + i / Q) * C + q * 4;
+    const float4 g = ld4(dz + off), v = ld4(y + off);
+    const float4 c01 = ld4(coef + q * 8), c23 = ld4(coef + q * 8 + 4);
+    const float4 s01 = ld4(saved + q * 8), s23 = ld4(saved + q * 8 + 4);
+    float4 s1, s2;
+#define TGB_BN_ACC(f, ca, cb, mu, rs)                                   \
+  {                                                                     \
+    const float dn = (!relu || fmaf(v.f, ca, cb) > 0.f) ? g.f : 0.f;    \
+    s1.f = dn;                                                          \
+    s2.f = dn * ((v.f - (mu)) * (rs));                                  \
+  }
+    TGB_BN_ACC(x, c01.x, c01.y, s01.x, s01.y)
+    TGB_BN_ACC(y, c01.z, c01.w, s01.z, s01.w)
+    TGB_BN_ACC(z, c23.x, c23.y, s23.x, s23.y)
+    TGB_BN_ACC(w, c23.z, c23.w, s23.z, s23.w)
+#undef TGB_BN_ACC
+    if (fixed) {
+      a1.x += s1.x; a1.y += s1.y; a1.z += s1.z; a1.w += s1.w;
+      a2.x += s2.x; a2.y += s2.y; a2.z += s2.z; a2.w += s2.w;
+    } else {
+      float* d = sh + q * 8;
+      atomicAdd(d + 0, s1.x); atomicAdd(d + 1, s2.x); atomicAdd(d + 2, s1.y); atomicAdd(d + 3, s2.y);
+      atomicAdd(d + 4, s1.z); atomicAdd(d + 5, s2.z); atomicAdd(d + 6, s1.w); atomicAdd(d + 7, s2.w);
+    }
+  }
+  if (fixed) {
+    float* d = sh + (threadIdx.x % Q) * 8;
+    atomicAdd(d + 0, a1.x); atomicAdd(d + 1, a2.x); atomicAdd(d + 2, a1.y); atomicAdd(d + 3, a2.y);
+    atomicAdd(d + 4, a1.z); atomicAdd(d + 5, a2.z); atomicAdd(d + 6, a1.w); atomicAdd(d + 7, a2.w);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(sums + i, sh[i]);
+}
+
+// dy = a * (dn - S1/P - xhat * S2/P)
+__global__ void __launch_bounds__(kEwThreads)
+bn_bwd_apply_kernel(const float* __restrict__ dz, const float* __restrict__ y,
+                    const float* __restrict__ coef, const float* __restrict__ saved,
+                    const float* __restrict__ sums, float* __restrict__ dy, size_t n4, int C,
+                    float inv_p, int relu) {
+  const int Q = C >> 2;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int q = static_cast<int>(i % Q);
+    const float4 g = ld4(dz + i * 4), v = ld4(y + i * 4);
+    const float4 c01 = ld4(coef + q * 8), c23 = ld4(coef + q * 8 + 4);
+    const float4 s01 = ld4(saved + q * 8), s23 = ld4(saved + q * 8 + 4);
+    const float4 m01 = ld4(sums + q * 8), m23 = ld4(sums + q * 8 + 4);
+    float4 o;
+#define TGB_BN_BWD(f, ca, cb, mu, rs, S1, S2)                           \
+  {                                                                     \
+    const float dn = (!relu || fmaf(v.f, ca, cb) > 0.f) ? g.f : 0.f;    \
+    const float xh = (v.f - (mu)) * (rs);                               \
+    o.f = (ca) * (dn - (S1) * inv_p - xh * (S2) * inv_p);               \
+  }
+    TGB_BN_BWD(x, c01.x, c01.y, s01.x, s01.y, m01.x, m01.y)
+    TGB_BN_BWD(y, c01.z, c01.w, s01.z, s01.w, m01.z, m01.w)
+    TGB_BN_BWD(z, c23.x, c23.y, s23.x, s23.y, m23.x, m23.y)
+    TGB_BN_BWD(w, c23.z, c23.w, s23.z, s23.w, m23.z, m23.w)
+#undef TGB_BN_BWD
+    st4(dy + i * 4, o);
+  }
+}
+
 static int ew_grid(size_t n4) {
   size_t blocks = (n4 + kEwThreads - 1) / kEwThreads;
   const size_t cap = static_cast<size_t>(sm_count()) * 16;
@@ -275,5 +403,44 @@ extern "C" int tgb_in_leaky_bwd(const float* dz, const float* z, const float* me
   dim3 grid(gx, G);
   in_backward_kernel<<<grid, kEwThreads, 0, stream>>>(dz, z, mean_coef, sums, dy, P, C, slope);
   TGB_CHECK_LAUNCH("in_leaky_bwd");
+  return 0;
+}
+
+extern "C" int tgb_bn_prepare(const float* stats, const float* gamma, const float* beta,
+                              float* coef, float* saved, float* running_mean,
+                              float* running_var, int P, int C, float eps, float momentum,
+                              cudaStream_t stream) {
+  const float unbias = P > 1 ? static_cast<float>(P) / static_cast<float>(P - 1) : 1.f;
+  bn_prepare_kernel<<<(C + 255) / 256, 256, 0, stream>>>(stats, gamma, beta, coef, saved,
+                                                        running_mean, running_var, C,
+                                                        1.f / static_cast<float>(P), unbias, eps,
+                                                        momentum);
+  TGB_CHECK_LAUNCH("bn_prepare");
+  return 0;
+}
+
+extern "C" int tgb_bn_act_fwd(const float* y, const float* coef, float* z, int P, int C, int relu,
+                              cudaStream_t stream) {
+  if (C % 4) return set_error("bn_act_fwd: C %% 4 != 0");
+  const size_t n4 = static_cast<size_t>(P) * (C / 4);
+  bn_apply_kernel<<<ew_grid(n4), kEwThreads, 0, stream>>>(y, coef, z, n4, C, relu);
+  TGB_CHECK_LAUNCH("bn_act_fwd");
+  return 0;
+}
+
+extern "C" int tgb_bn_act_bwd(const float* dz, const float* y, const float* coef,
+                              const float* saved, float* sums, float* dy, int P, int C, int relu,
+                              cudaStream_t stream) {
+  if (C % 4) return set_error("bn_act_bwd: C %% 4 != 0");
+  int slabs = sm_count() * 2;
+  if (slabs > (P + 63) / 64) slabs = (P + 63) / 64;
+  if (slabs < 1) slabs = 1;
+  bn_bwd_reduce_kernel<<<slabs, kEwThreads, 2 * C * sizeof(float), stream>>>(
+      dz, y, coef, saved, sums, P, C, slabs, relu);
+  TGB_CHECK_LAUNCH("bn_bwd_reduce");
+  const size_t n4 = static_cast<size_t>(P) * (C / 4);
+  bn_bwd_apply_kernel<<<ew_grid(n4), kEwThreads, 0, stream>>>(
+      dz, y, coef, saved, sums, dy, n4, C, 1.f / static_cast<float>(P), relu);
+  TGB_CHECK_LAUNCH("bn_bwd_apply");
   return 0;
 }

@@ -99,6 +99,25 @@ int tgb_in_leaky_bwd_sums(const float* dz, const float* z, float* out, int G, in
 int tgb_in_leaky_bwd(const float* dz, const float* z, const float* mean_coef, const float* sums,
                      float* dy, int G, int P, int C, float slope, cudaStream_t stream);
 
+/* Fused BatchNorm2d (training) + optional ReLU on [P = N*H*W][C] fp32, C % 4 == 0.
+ * tgb_bn_prepare: from per-channel (sum, sum of squares) `stats` [C][2] - taken from the
+ *   convolution epilogue (stats_mode 2) or tgb_moments - computes coef[c] = (a, b) with
+ *   bn(y) = y*a + b and saved[c] = (mean, rstd); when running_mean/var are given it also folds
+ *   the batch statistics into them exactly like nn.BatchNorm2d (unbiased running variance).
+ *   gamma/beta may be NULL (no affine).
+ * tgb_bn_act_fwd: z = act(y*a + b), act = ReLU if relu != 0.
+ * tgb_bn_act_bwd: zeroed `sums` [C][2] receives (sum dn, sum dn*xhat) = (dbeta, dgamma), then
+ *   dy = a * (dn - S1/P - xhat*S2/P); the ReLU mask and xhat are re-derived from y.
+ * Reference call sites: nn.BatchNorm2d (+ nn.ReLU) in benchmarks/models/resnet and amoebanet,
+ * F.batch_norm in torchgpipe/batchnorm.py:112-121 (cuDNN / ATen there). */
+int tgb_bn_prepare(const float* stats, const float* gamma, const float* beta, float* coef,
+                   float* saved, float* running_mean, float* running_var, int P, int C,
+                   float eps, float momentum, cudaStream_t stream);
+int tgb_bn_act_fwd(const float* y, const float* coef, float* z, int P, int C, int relu,
+                   cudaStream_t stream);
+int tgb_bn_act_bwd(const float* dz, const float* y, const float* coef, const float* saved,
+                   float* sums, float* dy, int P, int C, int relu, cudaStream_t stream);
+
 /* Fused gradient all-reduce across data-parallel replicas: out = scale * sum over replicas, in
  * place in every replica's fp32 bucket, optionally also as a local bf16 copy. One kernel per
  * rank: barrier, reduce-scatter (P2P loads from the peers' buckets, or multimem.ld_reduce through

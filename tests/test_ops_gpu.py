@@ -269,3 +269,95 @@ def test_cuda_graph_recompute_reproduces_dropout_mask():
         assert torch.isfinite(gin).all()
         masks.append((out == 0).all(dim=3).all(dim=2))
     assert masks[0].any() and not torch.equal(masks[0], masks[1])   # a fresh mask every step
+
+
+@pytest.mark.parametrize('relu', [False, True])
+@pytest.mark.parametrize('C,H,W', [(64, 14, 14), (36, 7, 5), (2048, 4, 4)])
+def test_batchnorm_act_fwd_bwd(C, H, W, relu):
+    from torchgpipe_b200.ops import functional as TF
+    torch.manual_seed(21)
+    N = 6
+    y = (torch.randn(N, C, H, W, device='cuda') * 2 + 0.5).contiguous(memory_format=CL)
+    y.requires_grad_()
+    bn = nn.BatchNorm2d(C).cuda()
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5)
+        bn.bias.uniform_(-0.5, 0.5)
+    rm, rv = bn.running_mean.clone(), bn.running_var.clone()
+    w = bn.weight.detach().clone().requires_grad_()
+    b = bn.bias.detach().clone().requires_grad_()
+    z = TF.batchnorm_act(y, None, w, b, rm, rv, bn.eps, bn.momentum, relu)
+
+    yr = y.detach().clone().requires_grad_()
+    zr = bn(yr)
+    zr = F.relu(zr) if relu else zr
+    assert torch.allclose(z, zr, rtol=1e-4, atol=1e-4)
+    assert torch.allclose(rm, bn.running_mean, atol=1e-5)
+    assert torch.allclose(rv, bn.running_var, rtol=1e-4, atol=1e-5)
+
+    g = torch.randn_like(zr)
+    dy, dw, db = torch.autograd.grad(z, (y, w, b), g)
+    dyr, dwr, dbr = torch.autograd.grad(zr, (yr, bn.weight, bn.bias), g)
+    assert rel_err(dy, dyr) < 1e-3
+    assert rel_err(dw, dwr) < 1e-3 and rel_err(db, dbr) < 1e-3
+
+
+@pytest.mark.parametrize('stride', [1, 2])
+def test_conv_bn_relu_module_matches_unfused(stride):
+    from torchgpipe_b200 import ops
+    torch.manual_seed(22)
+    plain = nn.Sequential(nn.Conv2d(64, 128, 3, stride=stride, padding=1, bias=False),
+                          nn.BatchNorm2d(128), nn.ReLU()).cuda()
+    fused = ops.convert_to_sm100(copy.deepcopy(plain))
+    assert type(fused[0]).__name__ == 'ConvBatchNormAct'
+    assert list(fused.state_dict().keys()) == list(plain.state_dict().keys())
+    x = torch.randn(4, 64, 16, 16, device='cuda', requires_grad=True)
+    xr = x.detach().clone().requires_grad_()
+    z, zr = fused(x), plain(xr)
+    assert rel_err(z, zr) < 3e-3
+    assert torch.allclose(fused[1].running_mean, plain[1].running_mean, atol=1e-3)
+    assert torch.allclose(fused[1].running_var, plain[1].running_var, rtol=1e-2, atol=1e-3)
+    assert int(fused[1].num_batches_tracked) == 1
+    g = torch.randn_like(zr)
+    z.backward(g)
+    zr.backward(g)
+    assert rel_err(x.grad, xr.grad) < 2e-2
+    assert rel_err(fused[0].weight.grad, plain[0].weight.grad) < 2e-2
+    assert rel_err(fused[1].weight.grad, plain[1].weight.grad) < 2e-2
+    fused.eval()
+    plain.eval()
+    assert rel_err(fused(x), plain(xr)) < 3e-3
+
+
+def test_absorbed_batchnorm_deferred_statistics():
+    from torchgpipe_b200 import ops
+    from torchgpipe_b200.batchnorm import DeferredBatchNorm
+    torch.manual_seed(23)
+    plain = nn.Sequential(nn.Conv2d(32, 64, 3, padding=1, bias=False), nn.BatchNorm2d(64)).cuda()
+    fused = ops.convert_to_sm100(copy.deepcopy(plain))
+    fused = DeferredBatchNorm.convert_deferred_batch_norm(fused, chunks=2)
+    assert fused[1].deferred_chunks == 2 and 'sum' in dict(fused[1].named_buffers())
+    x = torch.randn(8, 32, 12, 12, device='cuda') * 3
+    plain(x)                                    # full mini-batch statistics
+    for c in x.chunk(2):
+        fused(c)
+    assert int(fused[1].num_batches_tracked) == 1 and fused[1].tracked == 0
+    assert torch.allclose(fused[1].running_mean, plain[1].running_mean, atol=1e-3)
+    assert torch.allclose(fused[1].running_var, plain[1].running_var, rtol=2e-2, atol=1e-3)
+
+
+def test_converted_small_resnet_matches_plain():
+    from torchgpipe_b200 import ops
+    from torchgpipe_b200.models.resnet import build_resnet
+    torch.manual_seed(24)
+    plain = build_resnet([1, 1, 1, 1], num_classes=10).cuda()
+    fused = ops.convert_to_sm100(copy.deepcopy(plain))
+    assert len(fused) == len(plain)
+    x = torch.randn(4, 3, 64, 64, device='cuda')
+    out, ref = fused(x), plain(x)
+    assert rel_err(out, ref) < 2e-2
+    out.square().mean().backward()
+    ref.square().mean().backward()
+    for (n, p), (_, q) in zip(fused.named_parameters(), plain.named_parameters()):
+        cos = F.cosine_similarity(p.grad.flatten(), q.grad.flatten(), dim=0).item()
+        assert cos > 0.97, (n, cos)

@@ -129,6 +129,13 @@ class DeferredBatchNorm(_BatchNorm):
         if isinstance(module, DeferredBatchNorm) and module.chunks is chunks:
             return cast(TModule, module)
 
+        # A BatchNorm whose arithmetic lives in a fused sm_100a layer keeps running there; it
+        # only switches to mini-batch statistics tracking.
+        if hasattr(module, 'make_deferred'):
+            if getattr(module, 'track_running_stats', False):
+                module.make_deferred(chunks)  # type: ignore[operator]
+            return cast(TModule, module)
+
         converted: nn.Module = module
 
         if isinstance(module, _BatchNorm) and module.track_running_stats:

@@ -11,7 +11,8 @@ from typing import List, Tuple
 
 from torch import nn
 
-from torchgpipe_b200.ops.modules import Absorbed, Conv2dTC, ConvInstNormLeaky
+from torchgpipe_b200.ops.modules import (Absorbed, AbsorbedBatchNorm2d, Conv2dTC,
+                                         ConvBatchNormAct, ConvInstNormLeaky)
 
 __all__ = ['convert_to_sm100']
 
@@ -32,11 +33,23 @@ def _match_unet_cell(layers: List[Tuple[str, nn.Module]], i: int) -> bool:
             and isinstance(act, nn.LeakyReLU) and act.negative_slope > 0)
 
 
-def convert_to_sm100(module: nn.Module) -> nn.Module:
-    """Returns ``module`` with its hot layers running on the hand-written sm_100a kernels."""
-    if not isinstance(module, nn.Sequential):
-        return module
+def _match_conv_bn(layers: List[Tuple[str, nn.Module]], i: int) -> int:
+    """0 = no match, 2 = conv+bn, 3 = conv+bn+relu starting at ``layers[i]``."""
+    if i + 1 >= len(layers):
+        return 0
+    conv, bn = layers[i][1], layers[i + 1][1]
+    if not (isinstance(conv, nn.Conv2d) and conv.bias is None and conv.groups == 1
+            and conv.dilation == (1, 1) and conv.padding_mode == 'zeros'
+            and not isinstance(conv.padding, str) and conv.out_channels % 4 == 0):
+        return 0
+    if type(bn) is not nn.BatchNorm2d or bn.num_features != conv.out_channels:
+        return 0
+    if i + 2 < len(layers) and type(layers[i + 2][1]) is nn.ReLU:
+        return 3
+    return 2
 
+
+def _convert_sequential(module: nn.Sequential) -> nn.Sequential:
     layers = list(module.named_children())
     out: 'OrderedDict[str, nn.Module]' = OrderedDict()
     i = 0
@@ -49,9 +62,45 @@ def convert_to_sm100(module: nn.Module) -> nn.Module:
                 out[layers[i + k][0]] = Absorbed(layers[i + k][1], into=name)
             i += 4
             continue
-        if _plain_conv(layer) and layer.in_channels % 4 == 0 and layer.out_channels % 32 == 0:
-            out[name] = Conv2dTC(layer)
-        else:
-            out[name] = layer
+        n = _match_conv_bn(layers, i)
+        if n:
+            conv, bn = layers[i][1], layers[i + 1][1]
+            bn.__class__ = AbsorbedBatchNorm2d      # same object: parameters, buffers, keys stay
+            out[name] = ConvBatchNormAct(conv, bn, relu=(n == 3))
+            out[layers[i + 1][0]] = bn
+            if n == 3:
+                out[layers[i + 2][0]] = Absorbed(layers[i + 2][1], into=name)
+            i += n
+            continue
+        out[name] = _convert_any(layer)
         i += 1
-    return nn.Sequential(out)
+    converted = nn.Sequential(out)
+    converted.train(module.training)
+    return converted
+
+
+def _convert_any(module: nn.Module) -> nn.Module:
+    """Recursive rewrite of an arbitrary module tree (names of all children are preserved)."""
+    if isinstance(module, (ConvInstNormLeaky, ConvBatchNormAct, Conv2dTC, Absorbed,
+                           AbsorbedBatchNorm2d)):
+        return module
+    if type(module) is nn.Sequential:
+        return _convert_sequential(module)
+    if _plain_conv(module) and module.in_channels % 4 == 0 and module.out_channels % 32 == 0:
+        return Conv2dTC(module)         # type: ignore[arg-type]
+    for name, child in list(module.named_children()):
+        new = _convert_any(child)
+        if new is not child:
+            setattr(module, name, new)
+    return module
+
+
+def convert_to_sm100(module: nn.Module) -> nn.Module:
+    """Returns ``module`` with its hot layers running on the hand-written sm_100a kernels.
+
+    Recognised runs inside every (nested) ``nn.Sequential``:
+    ``Conv2d, Dropout2d, InstanceNorm2d, LeakyReLU`` (U-Net cell) and ``Conv2d, BatchNorm2d
+    [, ReLU]`` (ResNet / AmoebaNet); any other stride-1 convolution with suitable channel counts
+    becomes a :class:`Conv2dTC`. Number, order and names of layers and parameters never change.
+    """
+    return _convert_any(module)

@@ -14,7 +14,7 @@ from torch import Tensor
 from torchgpipe_b200.ops import _lib
 
 __all__ = ['conv2d', 'conv2d_forward', 'instnorm_leaky', 'channel_moments', 'conv_supported',
-           'refresh_dgrad_weight']
+           'refresh_dgrad_weight', 'batchnorm_act']
 
 _CL = torch.channels_last
 _c_int = ctypes.c_int
@@ -226,3 +226,72 @@ def instnorm_leaky(y: Tensor, stats: Optional[Tensor] = None, drop_scale: Option
     dropout). ``slope`` must be positive.
     """
     return _InstNormLeaky.apply(y, stats, drop_scale, float(eps), float(slope))
+
+
+class _BatchNormAct(torch.autograd.Function):
+    """z = act(BatchNorm(y)) in training mode from precomputed per-channel (sum, sum of squares).
+
+    Saves the convolution output ``y`` and two ``[C,2]`` tables; the ReLU mask and the
+    normalised activation are re-derived from ``y`` in backward.
+    """
+
+    @staticmethod
+    def forward(ctx, y: Tensor, stats: Tensor, weight: Optional[Tensor],  # type: ignore[override]
+                bias: Optional[Tensor], running_mean: Optional[Tensor],
+                running_var: Optional[Tensor], eps: float, momentum: float, relu: bool):
+        lib = _lib.require()
+        y = _cl(y)
+        N, C, H, W = y.shape
+        P = N * H * W
+        coef = torch.empty((C, 2), device=y.device, dtype=torch.float32)
+        saved = torch.empty((C, 2), device=y.device, dtype=torch.float32)
+        z = torch.empty_like(y, memory_format=_CL)
+        with torch.cuda.device(y.device):
+            st = _lib.stream_ptr(y.device)
+            rc = lib.tgb_bn_prepare(_lib.ptr(stats), _lib.ptr(weight), _lib.ptr(bias),
+                                    _lib.ptr(coef), _lib.ptr(saved), _lib.ptr(running_mean),
+                                    _lib.ptr(running_var), _c_int(P), _c_int(C), _c_float(eps),
+                                    _c_float(momentum), st)
+            _lib.check(rc, 'tgb_bn_prepare')
+            rc = lib.tgb_bn_act_fwd(_lib.ptr(y), _lib.ptr(coef), _lib.ptr(z), _c_int(P),
+                                    _c_int(C), _c_int(int(relu)), st)
+            _lib.check(rc, 'tgb_bn_act_fwd')
+        ctx.save_for_backward(y, coef, saved)
+        ctx.relu = relu
+        ctx.affine = (weight is not None, bias is not None)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz: Tensor):  # type: ignore[override]
+        lib = _lib.require()
+        y, coef, saved = ctx.saved_tensors
+        dz = _cl(dz)
+        N, C, H, W = y.shape
+        P = N * H * W
+        sums = torch.zeros((C, 2), device=y.device, dtype=torch.float32)
+        dy = torch.empty_like(y, memory_format=_CL)
+        with torch.cuda.device(y.device):
+            rc = lib.tgb_bn_act_bwd(_lib.ptr(dz), _lib.ptr(y), _lib.ptr(coef), _lib.ptr(saved),
+                                    _lib.ptr(sums), _lib.ptr(dy), _c_int(P), _c_int(C),
+                                    _c_int(int(ctx.relu)), _lib.stream_ptr(y.device))
+        _lib.check(rc, 'tgb_bn_act_bwd')
+        dweight = sums[:, 1].clone() if ctx.affine[0] else None
+        dbias = sums[:, 0].clone() if ctx.affine[1] else None
+        return dy, None, dweight, dbias, None, None, None, None, None
+
+
+def batchnorm_act(y: Tensor, stats: Optional[Tensor], weight: Optional[Tensor],
+                  bias: Optional[Tensor], running_mean: Optional[Tensor] = None,
+                  running_var: Optional[Tensor] = None, eps: float = 1e-5,
+                  momentum: float = 0.1, relu: bool = False) -> Tensor:
+    """Fused training-mode ``ReLU?(BatchNorm2d(y))``.
+
+    ``stats``: per-channel ``[C,2]`` (sum, sum of squares) from the convolution epilogue
+    (``stats_mode=2``); computed here when ``None``. When ``running_mean``/``running_var`` are
+    given they are updated in place like ``nn.BatchNorm2d`` does (pass ``None`` to skip, e.g.
+    during checkpoint recomputation or under DeferredBatchNorm).
+    """
+    if stats is None or stats.numel() == 0:
+        stats = channel_moments(y)
+    return _BatchNormAct.apply(y, stats, weight, bias, running_mean, running_var, float(eps),
+                               float(momentum), bool(relu))

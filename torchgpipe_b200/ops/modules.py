@@ -5,9 +5,10 @@ import torch
 from torch import Tensor, nn
 import torch.nn.functional as F
 
+from torchgpipe_b200.checkpoint import is_recomputing
 from torchgpipe_b200.ops import functional as TF
 
-__all__ = ['Absorbed', 'ConvInstNormLeaky', 'Conv2dTC']
+__all__ = ['Absorbed', 'ConvInstNormLeaky', 'Conv2dTC', 'ConvBatchNormAct', 'AbsorbedBatchNorm2d']
 
 _CL = torch.channels_last
 
@@ -110,3 +111,121 @@ class ConvInstNormLeaky(nn.Module):
             x = input.contiguous(memory_format=_CL)
             y, stats = F.conv2d(x, self.weight, None, padding=self.padding), None
         return TF.instnorm_leaky(y, stats, scale, self.eps, self.slope)
+
+
+class AbsorbedBatchNorm2d(nn.BatchNorm2d):
+    """A ``BatchNorm2d`` whose arithmetic has moved into the preceding :class:`ConvBatchNormAct`.
+
+    The instance keeps owning its parameters and running statistics (so ``state_dict`` keys do
+    not change) but its ``forward`` is the identity. ``deferred_chunks > 0`` switches the owner
+    to DeferredBatchNorm semantics: statistics are accumulated over that many micro-batches
+    (buffers ``sum`` / ``sum_squares``, as in reference ``torchgpipe/batchnorm.py:33-34``) and the
+    running estimates are committed once per mini-batch.
+    """
+
+    deferred_chunks = 0
+    counter = 0
+    tracked = 0
+
+    def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
+        return input
+
+    def extra_repr(self) -> str:
+        extra = super().extra_repr() + ', absorbed'
+        if self.deferred_chunks:
+            extra += f', deferred over {self.deferred_chunks} micro-batches'
+        return extra
+
+    def make_deferred(self, chunks: int) -> None:
+        if 'sum' not in self._buffers:
+            self.register_buffer('sum', torch.zeros_like(self.running_mean))
+            self.register_buffer('sum_squares', torch.zeros_like(self.running_var))
+        self.deferred_chunks = chunks
+        self.counter = self.tracked = 0
+
+    def track(self, stats: Tensor, count: int) -> None:
+        """Adds one micro-batch's (sum, sum of squares); commits after ``deferred_chunks``."""
+        with torch.no_grad():
+            self.sum += stats[:, 0]
+            self.sum_squares += stats[:, 1]
+            self.counter += count
+            self.tracked += 1
+            if self.tracked == self.deferred_chunks:
+                self.num_batches_tracked += 1
+                factor = (1.0 / float(self.num_batches_tracked) if self.momentum is None
+                          else self.momentum)
+                mean = self.sum / self.counter
+                var = self.sum_squares / self.counter - mean ** 2      # biased, as the reference
+                self.running_mean.mul_(1 - factor).add_(mean * factor)
+                self.running_var.mul_(1 - factor).add_(var * factor)
+                self.sum.zero_()
+                self.sum_squares.zero_()
+                self.counter = self.tracked = 0
+
+
+class ConvBatchNormAct(nn.Module):
+    """``Conv2d(bias=False) -> BatchNorm2d [-> ReLU]`` with the statistics taken in the
+    convolution's epilogue and one normalise(+ReLU) pass (reference: separate cuDNN conv, BN and
+    ATen ReLU kernels in ``benchmarks/models/resnet`` / ``amoebanet``).
+
+    The BatchNorm layer stays in the model as an :class:`AbsorbedBatchNorm2d` that owns the affine
+    parameters and running statistics; this module only *uses* them.
+    """
+
+    def __init__(self, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool) -> None:
+        super().__init__()
+        self.in_channels, self.out_channels = conv.in_channels, conv.out_channels
+        self.kernel_size, self.padding, self.stride = conv.kernel_size, conv.padding, conv.stride
+        self.weight = conv.weight
+        self.weight.data = self.weight.data.contiguous(memory_format=_CL)
+        self.relu = bool(relu)
+        self._bn = (bn,)            # a tuple hides it from nn.Module registration
+        self._cache: dict = {}
+
+    @property
+    def bn(self) -> AbsorbedBatchNorm2d:
+        return self._bn[0]  # type: ignore[return-value]
+
+    def refresh_derived_weights(self) -> None:
+        TF.refresh_dgrad_weight(self.weight, self._cache)
+
+    def extra_repr(self) -> str:
+        return (f'{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, '
+                f'stride={self.stride}, padding={self.padding}, bn(eps={self.bn.eps}), '
+                f'relu={self.relu}, tcgen05/tf32')
+
+    def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
+        bn = self.bn
+        native = (input.is_cuda and input.dtype == torch.float32
+                  and self.out_channels % 4 == 0)
+        if not native or not bn.training:
+            y = F.conv2d(input, self.weight, None, self.stride, self.padding)
+            use_batch_stats = bn.training or bn.running_mean is None
+            y = F.batch_norm(y, None if use_batch_stats else bn.running_mean,
+                             None if use_batch_stats else bn.running_var, bn.weight, bn.bias,
+                             use_batch_stats, 0.0, bn.eps)
+            return F.relu(y) if self.relu else y
+
+        if self.stride == (1, 1) and TF.conv_supported(self.in_channels, self.out_channels,
+                                                       1, 1, 1):
+            y, stats = TF.conv2d(input, self.weight, self.padding, stats_mode=2,
+                                 cache=self._cache)
+        else:
+            # strided / odd-channel convolutions: library kernel, statistics by tgb_moments
+            x = input.contiguous(memory_format=_CL)
+            y = F.conv2d(x, self.weight, None, self.stride, self.padding)
+            stats = TF.channel_moments(y)
+
+        running_mean = running_var = None
+        momentum = 0.0
+        recomputing = is_recomputing()
+        if bn.track_running_stats and not recomputing:
+            if bn.deferred_chunks:
+                bn.track(stats, y.numel() // y.size(1))
+            else:
+                bn.num_batches_tracked += 1
+                momentum = (1.0 / float(bn.num_batches_tracked) if bn.momentum is None
+                            else bn.momentum)
+                running_mean, running_var = bn.running_mean, bn.running_var
+        return TF.batchnorm_act(y, stats, bn.weight, bn.bias, running_mean, running_var, bn.eps,
+                                momentum, self.relu)
