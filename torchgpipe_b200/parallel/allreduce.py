@@ -38,6 +38,15 @@ class SymmetricBuffer:
                                                                      torch.cuda.current_device())
         align = 4 * self.world
         self.numel = (numel + align - 1) // align * align
+        enable = getattr(symm_mem, 'enable_symm_mem_for_group', None)
+        if enable is not None:
+            try:
+                import warnings
+                with warnings.catch_warnings():
+                    warnings.simplefilter('ignore')
+                    enable(self.group.group_name)
+            except Exception:
+                pass            # newer releases enable groups implicitly
         self.tensor = symm_mem.empty(self.numel, dtype=torch.float32, device=self.device)
         self.tensor.zero_()
         self.handle = symm_mem.rendezvous(self.tensor, self.group)
