@@ -305,7 +305,13 @@ static int launch_wgrad(const CUtensorMap& mdy, const CUtensorMap& mx, const Wgr
                         float* out, int grid, cudaStream_t stream) {
   using L = WgSmem<BN, STAGES>;
   constexpr int smem_bytes = L::kTotal + 1024;
-  static bool configured = false;
+  // the opt-in shared-memory size is a per-device attribute of the kernel: one process may
+  // drive several GPUs (single-process GPipe), so remember it per device
+  static bool configured_on[64] = {false};
+  int dev_ = 0;
+  cudaGetDevice(&dev_);
+  if (dev_ < 0 || dev_ >= 64) dev_ = 0;
+  bool& configured = configured_on[dev_];
   auto kern = conv_wgrad_tf32_kernel<BN, STAGES>;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,

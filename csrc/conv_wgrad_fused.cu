@@ -270,7 +270,13 @@ static int launch_fused(const CUtensorMap& mdy, const CUtensorMap& mx, const Wgr
                         float* out, int grid, cudaStream_t stream) {
   using L = WfCfg<BN>;
   constexpr int smem_bytes = L::kTotal + 1024;
-  static bool configured = false;
+  // the opt-in shared-memory size is a per-device attribute of the kernel: one process may
+  // drive several GPUs (single-process GPipe), so remember it per device
+  static bool configured_on[64] = {false};
+  int dev_ = 0;
+  cudaGetDevice(&dev_);
+  if (dev_ < 0 || dev_ >= 64) dev_ = 0;
+  bool& configured = configured_on[dev_];
   auto kern = conv_wgrad_fused_kernel<BN>;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,

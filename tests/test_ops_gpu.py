@@ -361,3 +361,20 @@ def test_converted_small_resnet_matches_plain():
     for (n, p), (_, q) in zip(fused.named_parameters(), plain.named_parameters()):
         cos = F.cosine_similarity(p.grad.flatten(), q.grad.flatten(), dim=0).item()
         assert cos > 0.97, (n, cos)
+
+
+@pytest.mark.multigpu
+def test_native_kernels_on_second_device_in_one_process():
+    """Single-process GPipe drives several GPUs: per-device kernel attributes must be set on each."""
+    from torchgpipe_b200 import GPipe, ops
+    from torchgpipe_b200.models import unet
+    torch.manual_seed(30)
+    model = ops.convert_to_sm100(unet(depth=2, num_convs=2, base_channels=64))
+    n = len(model)
+    pipe = GPipe(model, [n // 2, n - n // 2], devices=['cuda:0', 'cuda:1'], chunks=2)
+    out = pipe(torch.rand(4, 3, 32, 32, device='cuda:0'))
+    assert out.device == torch.device('cuda', 1)
+    out.mean().backward()
+    torch.cuda.synchronize(0)
+    torch.cuda.synchronize(1)
+    assert all(torch.isfinite(p.grad).all() for p in pipe.parameters())
