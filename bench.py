@@ -40,10 +40,48 @@ EXPERIMENTS = {
         4: dict(batch=512, chunks=16, balance=[30, 66, 84, 61]),
         8: dict(batch=640, chunks=40, balance=[16, 27, 31, 44, 22, 57, 27, 17]),
     },
+    # reference benchmarks/amoebanetd-speed/main.py:50-96 (n{2,4,8}m32); it defines no 1-GPU run
+    'amoebanetd': {
+        2: dict(batch=1280, chunks=32, balance=[9, 15]),
+        4: dict(batch=1152, chunks=32, balance=[3, 6, 7, 8]),
+        8: dict(batch=1280, chunks=32, balance=[2, 2, 2, 3, 3, 4, 4, 4]),
+    },
 }
 # Reference's published P40 numbers for the same experiments.
-PUBLISHED = {'unet': {1: 24.456, 2: 35.502, 4: 67.042, 8: 88.497}}
+PUBLISHED = {'unet': {1: 24.456, 2: 35.502, 4: 67.042, 8: 88.497},
+             'amoebanetd': {2: 47.386, 4: 72.412, 8: 132.413}}
 INPUT_HW = 192
+MODEL_INFO = {'unet': dict(hw=192, name='U-Net (B=5,C=64) 241 layers 232.7M params',
+                           metric='U-Net(5,64)', loss='bce_with_logits'),
+              'amoebanetd': dict(hw=224, name='AmoebaNet-D (L=18,D=256) 24 layers 122.5M params',
+                                 metric='AmoebaNet-D(18,256)', loss='cross_entropy')}
+
+
+def build_model(builders, name):
+    if name == 'unet':
+        return builders['unet'](depth=5, num_convs=5, base_channels=64, input_channels=3,
+                                output_channels=1)
+    return builders['amoebanetd'](num_classes=1000, num_layers=18, num_filters=256)
+
+
+def make_target(torch, name, batch, hw, device):
+    if name == 'unet':
+        return torch.ones(batch, 1, hw, hw, device=device)
+    g = torch.Generator().manual_seed(1)
+    return torch.randint(1000, (batch,), generator=g).to(device)
+
+
+def loss_mean(F, name, output, target):
+    if name == 'unet':
+        return F.binary_cross_entropy_with_logits(output, target)
+    return F.cross_entropy(output, target)
+
+
+def loss_sum(F, name, output, target):
+    """Sum-reduced loss of one micro-batch (divide by the mini-batch normaliser outside)."""
+    if name == 'unet':
+        return F.binary_cross_entropy_with_logits(output, target, reduction='sum')
+    return F.cross_entropy(output, target, reduction='sum')
 
 
 # --------------------------------------------------------------------------- helpers
@@ -175,16 +213,17 @@ def run_ours(args):
 
     from torchgpipe_b200 import GPipe
     from torchgpipe_b200 import ops
-    from torchgpipe_b200.models import unet
+    from torchgpipe_b200.models import amoebanetd, unet
+    info = MODEL_INFO[args.model]
+    hw = info['hw']
 
     torch.manual_seed(0)
-    model = unet(depth=5, num_convs=5, base_channels=64, input_channels=3, output_channels=1)
+    model = build_model(dict(unet=unet, amoebanetd=amoebanetd), args.model)
     if not args.no_kernels:
         model = ops.convert_to_sm100(model)
 
     batch, chunks, balance = cfg['batch'], cfg['chunks'], cfg['balance']
-    numel_per_sample = INPUT_HW * INPUT_HW
-    host_input = torch.rand(batch, 3, INPUT_HW, INPUT_HW).pin_memory()
+    host_input = torch.rand(batch, 3, hw, hw).pin_memory()
     loss_host = torch.zeros(1).pin_memory()
 
     first, last = rank == 0, rank == world - 1
@@ -195,11 +234,11 @@ def run_ours(args):
         params = list(pipe.parameters())
         out_device = pipe.devices[-1]
         dev_input = host_input.to(device)
-        target = torch.ones(batch, 1, INPUT_HW, INPUT_HW, device=out_device)
+        target = make_target(torch, args.model, batch, hw, out_device)
 
         def step(inp=None):
             output = pipe(dev_input if inp is None else inp)
-            loss = F.binary_cross_entropy_with_logits(output, target)
+            loss = loss_mean(F, args.model, output, target)
             loss.backward()
             opt.step()
             opt.zero_grad()
@@ -213,13 +252,14 @@ def run_ours(args):
                                 cuda_graphs=not args.no_graphs)
         params = list(pipe.model().parameters())
         dev_input = host_input.to(device) if first else None
-        target = torch.ones(batch, 1, INPUT_HW, INPUT_HW, device=device) if last else None
-        total = float(batch * numel_per_sample)
+        target = make_target(torch, args.model, batch, hw, device) if last else None
+        # normaliser of the mini-batch mean loss: elements for BCE, samples for cross-entropy
+        total = float(batch * hw * hw) if args.model == 'unet' else float(batch)
 
         def step(inp=None):
             outs = pipe.forward((dev_input if inp is None else inp) if first else None)
             if last:
-                losses = [F.binary_cross_entropy_with_logits(o, t, reduction='sum') / total
+                losses = [loss_sum(F, args.model, o, t) / total
                           for o, t in zip(outs, target.chunk(chunks))]
                 pipe.backward(losses)
                 loss = torch.stack([x.detach() for x in losses]).sum()
@@ -285,16 +325,17 @@ def run_ours(args):
     value = samples / (ms / 1e3)
     e2e_value = samples / (e2e_wall / 1e3)
     result = {
-        'metric': 'U-Net(5,64) training throughput, GPipe pipeline-%d' % n,
+        'metric': '%s training throughput, GPipe pipeline-%d' % (MODEL_INFO[args.model]['metric'], n),
         'impl': 'ours',
         'value': value, 'unit': 'samples/s', 'n_gpus': n, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': value / PUBLISHED[args.model][n],
         'dtype': 'fp32 storage / tf32 tensor-core conv', 'data': 'synthetic',
-        'config': {'model': 'U-Net (B=5,C=64) 241 layers 232.7M params',
+        'config': {'model': MODEL_INFO[args.model]['name'],
                    'global_batch': batch, 'chunks': chunks, 'balance': balance,
-                   'input': [3, INPUT_HW, INPUT_HW], 'checkpoint': 'except_last',
-                   'optimizer': 'SGD(lr=0.1)', 'loss': 'bce_with_logits',
+                   'input': [3, MODEL_INFO[args.model]['hw'], MODEL_INFO[args.model]['hw']],
+                   'checkpoint': 'except_last',
+                   'optimizer': 'SGD(lr=0.1)', 'loss': MODEL_INFO[args.model]['loss'],
                    'parallelism': 'pp%d' % n,
                    'transport': 'single-process' if world == 1 else 'nccl-p2p',
                    'l2': 'flushed between steps (256 MiB write)',
@@ -336,7 +377,9 @@ def run_reference(args):
     import torchgpipe
     from torchgpipe import GPipe
     assert os.path.realpath(torchgpipe.__file__).startswith(os.path.realpath(ref_root))
-    from unet import unet  # reference model builder (benchmarks/models/unet)
+    from unet import unet  # reference model builders (benchmarks/models/*)
+    from amoebanet import amoebanetd
+    hw = MODEL_INFO[args.model]['hw']
 
     n = args.gpus
     cfg = EXPERIMENTS[args.model][n]
@@ -348,22 +391,22 @@ def run_reference(args):
     batch, chunks, balance = cfg['batch'], cfg['chunks'], cfg['balance']
     driver = rank == 0
     flush = L2Flusher(torch, device)
-    host_input = torch.rand(batch, 3, INPUT_HW, INPUT_HW).pin_memory()
+    host_input = torch.rand(batch, 3, hw, hw).pin_memory()
     loss_host = torch.zeros(1).pin_memory()
 
     if driver:
         torch.manual_seed(0)
-        model = unet(depth=5, num_convs=5, base_channels=64, input_channels=3, output_channels=1)
+        model = build_model(dict(unet=unet, amoebanetd=amoebanetd), args.model)
         devices = [torch.device('cuda', k) for k in range(n)]
         pipe = GPipe(model, balance, devices=devices, chunks=chunks)   # checkpoint default
         opt = SGD(pipe.parameters(), lr=0.1)
         dev_input = host_input.to(devices[0])
-        target = torch.ones(batch, 1, INPUT_HW, INPUT_HW, device=devices[-1])
+        target = make_target(torch, args.model, batch, hw, devices[-1])
         stage_in = torch.empty_like(dev_input)
 
         def step(inp=None):
             output = pipe(dev_input if inp is None else inp)
-            loss = F.binary_cross_entropy_with_logits(output, target)
+            loss = loss_mean(F, args.model, output, target)
             loss.backward()
             opt.step()
             opt.zero_grad()
@@ -432,16 +475,17 @@ def run_reference(args):
     samples = batch * args.steps
     value = samples / (ms / 1e3)
     result = {
-        'metric': 'U-Net(5,64) training throughput, GPipe pipeline-%d' % n,
+        'metric': '%s training throughput, GPipe pipeline-%d' % (MODEL_INFO[args.model]['metric'], n),
         'impl': 'reference',
         'value': value, 'unit': 'samples/s', 'n_gpus': n, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': value / PUBLISHED[args.model][n],
         'dtype': 'fp32 storage / tf32 cuDNN conv (PyTorch defaults)', 'data': 'synthetic',
-        'config': {'model': 'U-Net (B=5,C=64) 241 layers 232.7M params',
+        'config': {'model': MODEL_INFO[args.model]['name'],
                    'global_batch': batch, 'chunks': chunks, 'balance': balance,
-                   'input': [3, INPUT_HW, INPUT_HW], 'checkpoint': 'except_last',
-                   'optimizer': 'SGD(lr=0.1)', 'loss': 'bce_with_logits',
+                   'input': [3, MODEL_INFO[args.model]['hw'], MODEL_INFO[args.model]['hw']],
+                   'checkpoint': 'except_last',
+                   'optimizer': 'SGD(lr=0.1)', 'loss': MODEL_INFO[args.model]['loss'],
                    'parallelism': 'pp%d' % n, 'transport': 'single-process (reference GPipe)',
                    'l2': 'flushed between steps (256 MiB write)',
                    'torchgpipe': torchgpipe.__version__},
@@ -464,7 +508,8 @@ def main():
     p.add_argument('--steps', type=int, default=5)
     p.add_argument('--warmup', type=int, default=3)
     p.add_argument('--impl', choices=['ours', 'reference'], default='ours')
-    p.add_argument('--model', choices=['unet'], default='unet')
+    p.add_argument('--model', choices=['unet', 'amoebanetd'], default='unet',
+                   help='unet (default, headline) or amoebanetd (N in 2,4,8)')
     p.add_argument('--no-graphs', action='store_true',
                    help='ours arm, N>1: issue stage kernels eagerly instead of replaying CUDA graphs')
     p.add_argument('--no-kernels', action='store_true',

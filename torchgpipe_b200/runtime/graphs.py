@@ -77,6 +77,10 @@ class GraphedStage:
         self._captured: Dict[Signature, _Captured] = {}
         self._pool = None
         self._derived = [m for m in module.modules() if hasattr(m, 'refresh_derived_weights')]
+        # Buffers the forward graph updates in place (BatchNorm running statistics): the
+        # recomputation replay must not apply those updates a second time.
+        self._buffers = [b for b in module.buffers() if b.is_cuda]
+        self._shadow = [torch.empty_like(b) for b in self._buffers]
         self.replays = 0
         self.native_launches_replayed = 0
 
@@ -100,6 +104,8 @@ class GraphedStage:
 
             # Warm-up on a side stream: lazy initialisation (kernel attributes, caches, cuDNN
             # plans) must not happen inside a capture.
+            if self._buffers:
+                torch._foreach_copy_(self._shadow, self._buffers)   # warm-up must leave no trace
             side = torch.cuda.Stream(self.device)
             side.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(side):
@@ -110,6 +116,8 @@ class GraphedStage:
                     run_backward(outs, gouts)
                     del outs, gouts
             torch.cuda.current_stream(self.device).wait_stream(side)
+            if self._buffers:
+                torch._foreach_copy_(self._buffers, self._shadow)
             torch.cuda.synchronize(self.device)
 
             if self._pool is None:
@@ -185,7 +193,11 @@ class GraphedStage:
         if rng_state is not None:
             torch.cuda.set_rng_state(rng_state, self.device)
         self._load(cap.static_inputs, inputs)
+        if self._buffers:
+            torch._foreach_copy_(self._shadow, self._buffers)
         cap.fwd.replay()                         # checkpoint recomputation
+        if self._buffers:
+            torch._foreach_copy_(self._buffers, self._shadow)
         for s, g in zip(cap.static_grad_outputs, grad_outputs):
             if s is not None:
                 if g is None:
