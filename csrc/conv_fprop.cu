@@ -26,6 +26,8 @@
 #include "sm100_ptx.cuh"
 #include "tensormap.h"
 #include "tgb_internal.h"
+#include "../include/tgb200.h"
+#include <cstdlib>
 
 namespace tgb {
 
@@ -44,6 +46,7 @@ struct ConvGeom {
   int tiles_w, tiles_h, tiles_n, tiles_k;
   int c_blocks;
   int stats_mode;                   // 0 none, 1 per (n,k), 2 per k
+  int splits, iters_per_split;      // split of the reduction (taps x channel blocks) over CTAs
 };
 
 template <int BN, int STAGES>
@@ -79,7 +82,7 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int rows_valid = g.BW * g.BH * g.BNB;
-  const int num_tiles = g.tiles_w * g.tiles_h * g.tiles_n * g.tiles_k;
+  const int num_tiles = g.tiles_w * g.tiles_h * g.tiles_n * g.tiles_k * g.splits;
   const int k_iters = g.R * g.S * g.c_blocks;
   const uint32_t stage_tx = static_cast<uint32_t>(rows_valid * kBlockKBytes + L::kBBytes);
 
@@ -107,7 +110,14 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // A tile id also carries the reduction split: [it_begin, it_end) of the (tap, channel block)
+  // iterations. splits == 1 is the normal case.
+  int it_begin = 0, it_end = k_iters;
   auto decode_tile = [&](int tile, int& kt, int& tw, int& th, int& tn) {
+    const int ks = tile % g.splits;
+    tile /= g.splits;
+    it_begin = ks * g.iters_per_split;
+    it_end = min(k_iters, it_begin + g.iters_per_split);
     kt = tile % g.tiles_k;
     int rest = tile / g.tiles_k;
     tw = rest % g.tiles_w;
@@ -128,20 +138,24 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
         const int h0 = th * g.BH - g.pad_h;
         const int n0 = tn * g.BNB;
         const int k0 = kt * BN;
-        for (int tap = 0; tap < g.R * g.S; ++tap) {
+        int tap = it_begin / g.c_blocks;
+        int cb = it_begin - tap * g.c_blocks;
+        for (int it = it_begin; it < it_end; ++it) {
           const int r = tap / g.S;
           const int s = tap - r * g.S;
-          for (int cb = 0; cb < g.c_blocks; ++cb) {
-            mbar_wait(&empty_bar[stage], phase ^ 1);
-            uint8_t* a_dst = smem + stage * L::kStageBytes;
-            uint8_t* b_dst = a_dst + L::kABytes;
-            mbar_expect_tx(&full_bar[stage], stage_tx);
-            tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cb * kBlockK, w0 + s, h0 + r, n0);
-            tma_load_4d(b_dst, &tmap_w, &full_bar[stage], cb * kBlockK, tap, k0, 0);
-            if (++stage == STAGES) {
-              stage = 0;
-              phase ^= 1;
-            }
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* a_dst = smem + stage * L::kStageBytes;
+          uint8_t* b_dst = a_dst + L::kABytes;
+          mbar_expect_tx(&full_bar[stage], stage_tx);
+          tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cb * kBlockK, w0 + s, h0 + r, n0);
+          tma_load_4d(b_dst, &tmap_w, &full_bar[stage], cb * kBlockK, tap, k0, 0);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+          if (++cb == g.c_blocks) {
+            cb = 0;
+            ++tap;
           }
         }
       }
@@ -156,10 +170,13 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int kt_, tw_, th_, tn_;
+        decode_tile(tile, kt_, tw_, th_, tn_);            // sets [it_begin, it_end)
+        const int n_it = it_end - it_begin;
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
-        for (int it = 0; it < k_iters; ++it) {
+        for (int it = 0; it < n_it; ++it) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
@@ -173,7 +190,7 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
                         (it > 0 || k > 0) ? 1u : 0u);
           }
           mma_commit(&empty_bar[stage]);                  // smem slot free once MMAs retire
-          if (it == k_iters - 1) mma_commit(&tmem_full[acc]);
+          if (it == n_it - 1) mma_commit(&tmem_full[acc]);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -248,8 +265,12 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
         fence_proxy_async_smem();
         asm volatile("bar.sync 1, 128;" ::: "memory");
         if (epi_tid == 0) {
-          tma_store_4d(&tmap_y, buf, kt * BN + j * kEpiChunk, tw * g.BW, th * g.BH,
-                       tn * g.BNB);
+          if (g.splits > 1)       // partial sum of this reduction split: add into the zeroed Y
+            tma_reduce_add_4d(&tmap_y, buf, kt * BN + j * kEpiChunk, tw * g.BW, th * g.BH,
+                              tn * g.BNB);
+          else
+            tma_store_4d(&tmap_y, buf, kt * BN + j * kEpiChunk, tw * g.BW, th * g.BH,
+                         tn * g.BNB);
           tma_store_commit();
         }
         if (g.stats_mode != 0) {
@@ -372,7 +393,7 @@ static int launch_fprop(const CUtensorMap& mx, const CUtensorMap& mw, const CUte
                                            cudaGetErrorString(e));
     configured = true;
   }
-  const int num_tiles = g.tiles_w * g.tiles_h * g.tiles_n * g.tiles_k;
+  const int num_tiles = g.tiles_w * g.tiles_h * g.tiles_n * g.tiles_k * g.splits;
   const int grid = num_tiles < sm_count ? num_tiles : sm_count;
   kern<<<grid, kThreads, smem_bytes, stream>>>(mx, mw, my, g, stats);
   cudaError_t e = cudaGetLastError();
@@ -407,6 +428,28 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
   g.tiles_k = K / BN;
   g.c_blocks = (C + kBlockK - 1) / kBlockK;
   g.stats_mode = stats ? stats_mode : 0;
+  // Few output tiles and a long reduction (small images, many channels - e.g. 2048 ch at 6x6,
+  // or any layer at a small micro-batch): split the (tap, channel-block) loop over CTAs so the
+  // whole GPU works; partial sums are combined by TMA reduce-add into a zeroed Y.
+  const int sms = sm_count();
+  const int base_tiles = g.tiles_w * g.tiles_h * g.tiles_n * g.tiles_k;
+  const int k_iters = R * S * g.c_blocks;
+  g.splits = 1;
+  if (base_tiles * 2 <= sms && k_iters >= 32 && getenv("TGB_FPROP_NOSPLIT") == nullptr) {
+    int splits = sms / base_tiles;
+    if (splits > k_iters / 16) splits = k_iters / 16;
+    if (splits > 8) splits = 8;
+    if (splits > 1) g.splits = splits;
+  }
+  g.iters_per_split = (k_iters + g.splits - 1) / g.splits;
+  g.splits = (k_iters + g.iters_per_split - 1) / g.iters_per_split;
+  const bool stats_after = g.splits > 1 && g.stats_mode != 0;
+  const int stats_mode_req = g.stats_mode;
+  if (g.splits > 1) {
+    g.stats_mode = 0;         // partial tiles cannot produce sum of squares: tgb_moments below
+    cudaError_t e = cudaMemsetAsync(y, 0, static_cast<size_t>(N) * g.Ho * g.Wo * K * 4, stream);
+    if (e != cudaSuccess) return set_error("conv_fprop: memset: %s", cudaGetErrorString(e));
+  }
 
   CUtensorMap mx, mw, my;
   {
@@ -433,11 +476,17 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
     if (make_tensor_map(&my, y, 4, 4, dims, strides, box, 1))
       return set_error("conv_fprop: tensor map for Y failed");
   }
-  const int sms = sm_count();
+  int rc;
   switch (BN) {
-    case 256: return launch_fprop<256, 4>(mx, mw, my, g, stats, sms, stream);
-    case 128: return launch_fprop<128, 6>(mx, mw, my, g, stats, sms, stream);
-    case 64:  return launch_fprop<64, 8>(mx, mw, my, g, stats, sms, stream);
-    default:  return launch_fprop<32, 8>(mx, mw, my, g, stats, sms, stream);
+    case 256: rc = launch_fprop<256, 4>(mx, mw, my, g, stats, sms, stream); break;
+    case 128: rc = launch_fprop<128, 6>(mx, mw, my, g, stats, sms, stream); break;
+    case 64:  rc = launch_fprop<64, 8>(mx, mw, my, g, stats, sms, stream); break;
+    default:  rc = launch_fprop<32, 8>(mx, mw, my, g, stats, sms, stream); break;
   }
+  if (rc == 0 && stats_after) {
+    // Y is [N][Ho*Wo][K]: per-image (mode 1) or per-channel (mode 2) moments in one more pass
+    rc = stats_mode_req == 1 ? tgb_moments(y, stats, N, g.Ho * g.Wo, K, stream)
+                             : tgb_moments(y, stats, 1, N * g.Ho * g.Wo, K, stream);
+  }
+  return rc;
 }

@@ -324,6 +324,8 @@ int main(int argc, char** argv) {
       {"conv7x1", 2, 24, 8, 32, 64, 7, 1, 3, 0, 0},
       {"conv3x3_c512", 1, 8, 8, 512, 256, 3, 3, 1, 1, 0},
       {"conv3x3_c20", 1, 8, 8, 20, 32, 3, 3, 1, 1, 0},
+      {"conv3x3_splitk_in", 2, 6, 6, 256, 256, 3, 3, 1, 1, 1},
+      {"conv3x3_splitk_bn", 3, 12, 12, 512, 64, 3, 3, 1, 1, 2},
   };
   for (auto& c : small) {
     if (only && strcmp(only, c.name) && strcmp(only, "all")) continue;

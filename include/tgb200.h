@@ -118,6 +118,21 @@ int tgb_bn_act_fwd(const float* y, const float* coef, float* z, int P, int C, in
 int tgb_bn_act_bwd(const float* dz, const float* y, const float* coef, const float* saved,
                    float* sums, float* dy, int P, int C, int relu, cudaStream_t stream);
 
+/* NHWC fp32 data movement of the U-Net encoder / decoder (C, C1, C2 multiples of 4).
+ * tgb_maxpool2x2_fwd/bwd: MaxPool2d(2, stride 2); backward re-derives the arg-max from the saved
+ *   input x (first maximum in row-major window order, like ATen), no index tensor.
+ * tgb_upsample2x_cat_fwd: out[N,Hs,Ws,C1+C2] = concat(pad(nearest_x2(x[N,Hx,Wx,C1])), skip) in
+ *   one pass (reference: nn.Upsample + F.pad + torch.cat, benchmarks/models/unet/__init__.py:
+ *   27-39,131). _bwd writes dskip (contiguous) and dx (2x2 window sums) in one pass over dout.
+ * SURVEY K7 / K9 / K10 (ATen kernels in the reference). */
+int tgb_maxpool2x2_fwd(const float* x, float* y, int N, int H, int W, int C, cudaStream_t stream);
+int tgb_maxpool2x2_bwd(const float* x, const float* dy, float* dx, int N, int H, int W, int C,
+                       cudaStream_t stream);
+int tgb_upsample2x_cat_fwd(const float* x, const float* skip, float* out, int N, int Hx, int Wx,
+                           int C1, int Hs, int Ws, int C2, cudaStream_t stream);
+int tgb_upsample2x_cat_bwd(const float* dout, float* dx, float* dskip, int N, int Hx, int Wx,
+                           int C1, int Hs, int Ws, int C2, cudaStream_t stream);
+
 /* Fused gradient all-reduce across data-parallel replicas: out = scale * sum over replicas, in
  * place in every replica's fp32 bucket, optionally also as a local bf16 copy. One kernel per
  * rank: barrier, reduce-scatter (P2P loads from the peers' buckets, or multimem.ld_reduce through

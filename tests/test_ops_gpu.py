@@ -378,3 +378,50 @@ def test_native_kernels_on_second_device_in_one_process():
     torch.cuda.synchronize(0)
     torch.cuda.synchronize(1)
     assert all(torch.isfinite(p.grad).all() for p in pipe.parameters())
+
+
+@pytest.mark.parametrize('shape', [(3, 64, 16, 16), (2, 36, 9, 7), (1, 8, 2, 2)])
+def test_maxpool2x2_fwd_bwd(shape):
+    from torchgpipe_b200.ops import functional as TF
+    torch.manual_seed(31)
+    x = torch.randn(*shape, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    xr = x.detach().clone().requires_grad_()
+    y, yr = TF.maxpool2x2(x), F.max_pool2d(xr, 2, 2)
+    assert torch.equal(y, yr)
+    g = torch.randn_like(yr)
+    y.backward(g)
+    yr.backward(g)
+    assert torch.equal(x.grad, xr.grad)
+
+
+@pytest.mark.parametrize('hx,wx,hs,ws', [(8, 8, 16, 16), (5, 6, 11, 13)])
+def test_upsample2x_cat_fwd_bwd(hx, wx, hs, ws):
+    from torchgpipe_b200.ops import functional as TF
+    torch.manual_seed(32)
+    x = torch.randn(3, 32, hx, wx, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    s = torch.randn(3, 16, hs, ws, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    xr, sr = x.detach().clone().requires_grad_(), s.detach().clone().requires_grad_()
+    out = TF.upsample2x_cat(x, s)
+    up = F.interpolate(xr, scale_factor=2.0, mode='nearest')
+    up = F.pad(up, [0, ws - up.size(3), 0, hs - up.size(2)])
+    ref = torch.cat((up, sr), dim=1)
+    assert torch.equal(out, ref)
+    g = torch.randn_like(ref)
+    out.backward(g)
+    ref.backward(g)
+    assert torch.allclose(x.grad, xr.grad, atol=1e-6) and torch.equal(s.grad, sr.grad)
+
+
+def test_converted_unet_uses_fused_pool_and_upcat_across_stages():
+    from torchgpipe_b200 import GPipe, ops
+    from torchgpipe_b200.models import unet
+    torch.manual_seed(33)
+    plain = unet(depth=2, num_convs=1, base_channels=32).cuda().eval()
+    fused = ops.convert_to_sm100(copy.deepcopy(plain)).eval()
+    names = [type(m).__name__ for m in fused]
+    assert 'MaxPool2x2' in names and 'UpsamplePopCat' in names
+    x = torch.rand(2, 3, 32, 32, device='cuda')
+    ref = plain(x)
+    n = len(fused)
+    pipe = GPipe(fused, [n // 2, n - n // 2], devices=['cuda:0', 'cuda:0'], chunks=2).eval()
+    assert rel_err(pipe(x), ref) < 1e-2        # skip portals still route to the fused PopCat

@@ -12,7 +12,8 @@ from typing import List, Tuple
 from torch import nn
 
 from torchgpipe_b200.ops.modules import (Absorbed, AbsorbedBatchNorm2d, Conv2dTC,
-                                         ConvBatchNormAct, ConvInstNormLeaky)
+                                         ConvBatchNormAct, ConvInstNormLeaky, MaxPool2x2,
+                                         UpsamplePopCat)
 
 __all__ = ['convert_to_sm100']
 
@@ -49,6 +50,27 @@ def _match_conv_bn(layers: List[Tuple[str, nn.Module]], i: int) -> int:
     return 2
 
 
+def _is_maxpool2x2(m: nn.Module) -> bool:
+    def two(v):
+        return v == 2 or v == (2, 2)
+    return (type(m) is nn.MaxPool2d and two(m.kernel_size) and two(m.stride)
+            and m.padding in (0, (0, 0)) and m.dilation in (1, (1, 1)) and not m.ceil_mode
+            and not m.return_indices)
+
+
+def _match_upsample_popcat(layers: List[Tuple[str, nn.Module]], i: int) -> bool:
+    """``nn.Upsample(scale_factor=2, nearest)`` followed by the U-Net ``PopCat`` skippable."""
+    if i + 1 >= len(layers):
+        return False
+    up, nxt = layers[i][1], layers[i + 1][1]
+    if not (type(up) is nn.Upsample and up.mode == 'nearest' and up.size is None
+            and up.scale_factor in (2, 2.0, (2, 2), (2.0, 2.0))):
+        return False
+    from torchgpipe_b200.skip.skippable import Skippable
+    return (isinstance(nxt, Skippable) and type(nxt.module).__name__ == 'PopCat'
+            and nxt.poppable_names == frozenset(['skip']) and not nxt.stashable_names)
+
+
 def _convert_sequential(module: nn.Sequential) -> nn.Sequential:
     layers = list(module.named_children())
     out: 'OrderedDict[str, nn.Module]' = OrderedDict()
@@ -61,6 +83,18 @@ def _convert_sequential(module: nn.Sequential) -> nn.Sequential:
             for k in range(1, 4):
                 out[layers[i + k][0]] = Absorbed(layers[i + k][1], into=name)
             i += 4
+            continue
+        if _match_upsample_popcat(layers, i):
+            up, popcat = layers[i][1], layers[i + 1][1]
+            fused = UpsamplePopCat()
+            fused.namespaces = dict(popcat.namespaces)      # same skip route as the original
+            out[name] = Absorbed(up, into=layers[i + 1][0])
+            out[layers[i + 1][0]] = fused
+            i += 2
+            continue
+        if _is_maxpool2x2(layer):
+            out[name] = MaxPool2x2()
+            i += 1
             continue
         n = _match_conv_bn(layers, i)
         if n:
@@ -82,7 +116,7 @@ def _convert_sequential(module: nn.Sequential) -> nn.Sequential:
 def _convert_any(module: nn.Module) -> nn.Module:
     """Recursive rewrite of an arbitrary module tree (names of all children are preserved)."""
     if isinstance(module, (ConvInstNormLeaky, ConvBatchNormAct, Conv2dTC, Absorbed,
-                           AbsorbedBatchNorm2d)):
+                           AbsorbedBatchNorm2d, MaxPool2x2, UpsamplePopCat)):
         return module
     if type(module) is nn.Sequential:
         return _convert_sequential(module)

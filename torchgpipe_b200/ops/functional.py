@@ -14,7 +14,7 @@ from torch import Tensor
 from torchgpipe_b200.ops import _lib
 
 __all__ = ['conv2d', 'conv2d_forward', 'instnorm_leaky', 'channel_moments', 'conv_supported',
-           'refresh_dgrad_weight', 'batchnorm_act']
+           'refresh_dgrad_weight', 'batchnorm_act', 'maxpool2x2', 'upsample2x_cat']
 
 _CL = torch.channels_last
 _c_int = ctypes.c_int
@@ -295,3 +295,78 @@ def batchnorm_act(y: Tensor, stats: Optional[Tensor], weight: Optional[Tensor],
         stats = channel_moments(y)
     return _BatchNormAct.apply(y, stats, weight, bias, running_mean, running_var, float(eps),
                                float(momentum), bool(relu))
+
+
+class _MaxPool2x2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: Tensor):  # type: ignore[override]
+        lib = _lib.require()
+        x = _cl(x)
+        N, C, H, W = x.shape
+        y = torch.empty((N, C, H // 2, W // 2), device=x.device, dtype=torch.float32,
+                        memory_format=_CL)
+        with torch.cuda.device(x.device):
+            rc = lib.tgb_maxpool2x2_fwd(_lib.ptr(x), _lib.ptr(y), _c_int(N), _c_int(H), _c_int(W),
+                                        _c_int(C), _lib.stream_ptr(x.device))
+        _lib.check(rc, 'tgb_maxpool2x2_fwd')
+        ctx.save_for_backward(x)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy: Tensor):  # type: ignore[override]
+        lib = _lib.require()
+        x, = ctx.saved_tensors
+        dy = _cl(dy)
+        N, C, H, W = x.shape
+        dx = torch.empty_like(x, memory_format=_CL)
+        with torch.cuda.device(x.device):
+            rc = lib.tgb_maxpool2x2_bwd(_lib.ptr(x), _lib.ptr(dy), _lib.ptr(dx), _c_int(N),
+                                        _c_int(H), _c_int(W), _c_int(C),
+                                        _lib.stream_ptr(x.device))
+        _lib.check(rc, 'tgb_maxpool2x2_bwd')
+        return dx
+
+
+def maxpool2x2(x: Tensor) -> Tensor:
+    """``MaxPool2d(2, stride=2)`` on a channels-last fp32 CUDA tensor (C % 4 == 0)."""
+    return _MaxPool2x2.apply(x)
+
+
+class _UpsampleCat(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: Tensor, skip: Tensor):  # type: ignore[override]
+        lib = _lib.require()
+        x, skip = _cl(x), _cl(skip)
+        N, C1, Hx, Wx = x.shape
+        _, C2, Hs, Ws = skip.shape
+        out = torch.empty((N, C1 + C2, Hs, Ws), device=x.device, dtype=torch.float32,
+                          memory_format=_CL)
+        with torch.cuda.device(x.device):
+            rc = lib.tgb_upsample2x_cat_fwd(_lib.ptr(x), _lib.ptr(skip), _lib.ptr(out), _c_int(N),
+                                            _c_int(Hx), _c_int(Wx), _c_int(C1), _c_int(Hs),
+                                            _c_int(Ws), _c_int(C2), _lib.stream_ptr(x.device))
+        _lib.check(rc, 'tgb_upsample2x_cat_fwd')
+        ctx.dims = (N, Hx, Wx, C1, Hs, Ws, C2)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout: Tensor):  # type: ignore[override]
+        lib = _lib.require()
+        N, Hx, Wx, C1, Hs, Ws, C2 = ctx.dims
+        dout = _cl(dout)
+        dx = torch.empty((N, C1, Hx, Wx), device=dout.device, dtype=torch.float32,
+                         memory_format=_CL)
+        dskip = torch.empty((N, C2, Hs, Ws), device=dout.device, dtype=torch.float32,
+                            memory_format=_CL)
+        with torch.cuda.device(dout.device):
+            rc = lib.tgb_upsample2x_cat_bwd(_lib.ptr(dout), _lib.ptr(dx), _lib.ptr(dskip),
+                                            _c_int(N), _c_int(Hx), _c_int(Wx), _c_int(C1),
+                                            _c_int(Hs), _c_int(Ws), _c_int(C2),
+                                            _lib.stream_ptr(dout.device))
+        _lib.check(rc, 'tgb_upsample2x_cat_bwd')
+        return dx, dskip
+
+
+def upsample2x_cat(x: Tensor, skip: Tensor) -> Tensor:
+    """``cat(pad_to(upsample_nearest_x2(x), skip), skip, dim=1)`` in one pass (channels-last)."""
+    return _UpsampleCat.apply(x, skip)

@@ -8,7 +8,8 @@ import torch.nn.functional as F
 from torchgpipe_b200.checkpoint import is_recomputing
 from torchgpipe_b200.ops import functional as TF
 
-__all__ = ['Absorbed', 'ConvInstNormLeaky', 'Conv2dTC', 'ConvBatchNormAct', 'AbsorbedBatchNorm2d']
+__all__ = ['Absorbed', 'ConvInstNormLeaky', 'Conv2dTC', 'ConvBatchNormAct', 'AbsorbedBatchNorm2d',
+           'MaxPool2x2', 'UpsamplePopCat']
 
 _CL = torch.channels_last
 
@@ -229,3 +230,42 @@ class ConvBatchNormAct(nn.Module):
                 running_mean, running_var = bn.running_mean, bn.running_var
         return TF.batchnorm_act(y, stats, bn.weight, bn.bias, running_mean, running_var, bn.eps,
                                 momentum, self.relu)
+
+
+class MaxPool2x2(nn.Module):
+    """``nn.MaxPool2d(2, stride=2)`` on the NHWC kernel (index-free backward)."""
+
+    def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
+        if (input.is_cuda and input.dtype == torch.float32 and input.dim() == 4
+                and input.size(1) % 4 == 0):
+            return TF.maxpool2x2(input)
+        return F.max_pool2d(input, 2, 2)
+
+    def extra_repr(self) -> str:
+        return 'kernel_size=2, stride=2, nhwc'
+
+
+def _make_upsample_popcat():
+    from torchgpipe_b200.skip import pop, skippable
+
+    @skippable(pop=['skip'])
+    class UpsamplePopCat(nn.Module):
+        """Nearest x2 upsample of the input, pad to the popped skip tensor's size and concat
+        (input channels first) - ``nn.Upsample(scale_factor=2)`` followed by the reference's
+        ``PopCat`` - as one kernel. The preceding ``nn.Upsample`` layer becomes a placeholder."""
+
+        def forward(self, input: Tensor):  # type: ignore[override]
+            skipped = yield pop('skip')
+            if (input.is_cuda and input.dtype == torch.float32 and input.size(1) % 4 == 0
+                    and skipped.size(1) % 4 == 0):
+                return TF.upsample2x_cat(input, skipped)
+            up = F.interpolate(input, scale_factor=2.0, mode='nearest')
+            dh, dw = skipped.size(2) - up.size(2), skipped.size(3) - up.size(3)
+            if dh or dw:
+                up = F.pad(up, [0, dw, 0, dh])
+            return torch.cat((up, skipped), dim=1)
+
+    return UpsamplePopCat
+
+
+UpsamplePopCat = _make_upsample_popcat()
