@@ -409,8 +409,8 @@ using namespace tgb;
 extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, float* stats,
                                      int N, int H, int W, int C, int K, int R, int S, int pad_h,
                                      int pad_w, int stats_mode, cudaStream_t stream) {
-  if (C % 4 != 0 || K % 32 != 0)
-    return set_error("conv_fprop: need C %% 4 == 0 and K %% 32 == 0 (got C=%d K=%d)", C, K);
+  if (C % 4 != 0 || K % 4 != 0)
+    return set_error("conv_fprop: need C %% 4 == 0 and K %% 4 == 0 (got C=%d K=%d)", C, K);
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) |
        reinterpret_cast<uintptr_t>(y)) & 15)
     return set_error("conv_fprop: tensors must be 16-byte aligned");
@@ -421,11 +421,18 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
   g.Wo = W + 2 * pad_w - S + 1;
   if (g.Ho <= 0 || g.Wo <= 0) return set_error("conv_fprop: empty output");
   choose_pixel_box(N, g.Ho, g.Wo, g.BW, g.BH, g.BNB);
-  const int BN = (K % 256 == 0) ? 256 : (K % 128 == 0) ? 128 : (K % 64 == 0) ? 64 : 32;
+  // Output-channel tile: the widest of {256,128,64,32} that wastes at most 1/8 of its columns.
+  // A partial last tile is fine: weight rows past K are zero-filled by TMA and the store of
+  // columns past K is clipped.
+  int BN = 32;
+  for (int cand = 256; cand >= 32; cand /= 2) {
+    const int tiles = (K + cand - 1) / cand;
+    if ((tiles * cand - K) * 8 <= tiles * cand) { BN = cand; break; }
+  }
   g.tiles_w = (g.Wo + g.BW - 1) / g.BW;
   g.tiles_h = (g.Ho + g.BH - 1) / g.BH;
   g.tiles_n = (N + g.BNB - 1) / g.BNB;
-  g.tiles_k = K / BN;
+  g.tiles_k = (K + BN - 1) / BN;
   g.c_blocks = (C + kBlockK - 1) / kBlockK;
   g.stats_mode = stats ? stats_mode : 0;
   // Few output tiles and a long reduction (small images, many channels - e.g. 2048 ch at 6x6,

@@ -324,6 +324,9 @@ int main(int argc, char** argv) {
       {"conv7x1", 2, 24, 8, 32, 64, 7, 1, 3, 0, 0},
       {"conv3x3_c512", 1, 8, 8, 512, 256, 3, 3, 1, 1, 0},
       {"conv3x3_c20", 1, 8, 8, 20, 32, 3, 3, 1, 1, 0},
+      {"gemm1x1_k40", 2, 8, 8, 32, 40, 1, 1, 0, 0, 2},
+      {"conv3x3_k72", 1, 8, 8, 64, 72, 3, 3, 1, 1, 1},
+      {"linear_2048_1000", 40, 1, 1, 2048, 1000, 1, 1, 0, 0, 0},
       {"conv3x3_splitk_in", 2, 6, 6, 256, 256, 3, 3, 1, 1, 1},
       {"conv3x3_splitk_bn", 3, 12, 12, 512, 64, 3, 3, 1, 1, 2},
   };

@@ -23,7 +23,7 @@ void tgb_reset_launch_count(void);
 /* Stride-1 2-D convolution forward, TF32 tensor cores (tcgen05), FP32 accumulate.
  *   y[n,ho,wo,k] = sum_{r,s,c} x[n,ho+r-pad_h,wo+s-pad_w,c] * w[k,r,s,c]
  * x: [N,H,W,C]  w: [K,R,S,C]  y: [N,Ho,Wo,K], Ho = H+2*pad_h-R+1, Wo = W+2*pad_w-S+1.
- * Requires C % 4 == 0, K % 32 == 0, 16-byte aligned pointers.
+ * Requires C % 4 == 0, K % 4 == 0, 16-byte aligned pointers.
  * stats (optional, may be NULL): FP32 accumulators that the epilogue ADDS per-channel sum and
  * sum of squares of y into; the caller zeroes them first.
  *   stats_mode 1: [N][K][2] per (image, channel)  - InstanceNorm statistics

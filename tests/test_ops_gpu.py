@@ -43,6 +43,8 @@ CONV_CASES = [
     (1, 512, 8, 8, 256, 3, 3, 1, 1),
     (4, 64, 48, 48, 64, 3, 3, 1, 1),
     (2, 128, 24, 24, 32, 3, 3, 1, 1),
+    (2, 32, 8, 8, 40, 1, 1, 0, 0),          # output channels not a multiple of the tile
+    (1, 64, 8, 8, 72, 3, 3, 1, 1),
 ]
 
 
@@ -425,3 +427,21 @@ def test_converted_unet_uses_fused_pool_and_upcat_across_stages():
     n = len(fused)
     pipe = GPipe(fused, [n // 2, n - n // 2], devices=['cuda:0', 'cuda:0'], chunks=2).eval()
     assert rel_err(pipe(x), ref) < 1e-2        # skip portals still route to the fused PopCat
+
+
+def test_linear_on_conv_kernels():
+    from torchgpipe_b200 import ops
+    torch.manual_seed(40)
+    plain = nn.Linear(2048, 1000).cuda()
+    fused = ops.convert_to_sm100(nn.Sequential(copy.deepcopy(plain)))[0]
+    assert type(fused).__name__ == 'LinearTC'
+    x = torch.randn(40, 2048, device='cuda', requires_grad=True)
+    xr = x.detach().clone().requires_grad_()
+    y, yr = fused(x), plain(xr)
+    assert rel_err(y, yr) < 2e-3
+    g = torch.randn_like(yr)
+    y.backward(g)
+    yr.backward(g)
+    assert rel_err(x.grad, xr.grad) < 2e-3
+    assert rel_err(fused.weight.grad, plain.weight.grad) < 2e-3
+    assert rel_err(fused.bias.grad, plain.bias.grad) < 1e-5

@@ -12,8 +12,8 @@ from typing import List, Tuple
 from torch import nn
 
 from torchgpipe_b200.ops.modules import (Absorbed, AbsorbedBatchNorm2d, Conv2dTC,
-                                         ConvBatchNormAct, ConvInstNormLeaky, MaxPool2x2,
-                                         UpsamplePopCat)
+                                         ConvBatchNormAct, ConvInstNormLeaky, LinearTC,
+                                         MaxPool2x2, UpsamplePopCat)
 
 __all__ = ['convert_to_sm100']
 
@@ -116,12 +116,15 @@ def _convert_sequential(module: nn.Sequential) -> nn.Sequential:
 def _convert_any(module: nn.Module) -> nn.Module:
     """Recursive rewrite of an arbitrary module tree (names of all children are preserved)."""
     if isinstance(module, (ConvInstNormLeaky, ConvBatchNormAct, Conv2dTC, Absorbed,
-                           AbsorbedBatchNorm2d, MaxPool2x2, UpsamplePopCat)):
+                           AbsorbedBatchNorm2d, MaxPool2x2, UpsamplePopCat, LinearTC)):
         return module
     if type(module) is nn.Sequential:
         return _convert_sequential(module)
-    if _plain_conv(module) and module.in_channels % 4 == 0 and module.out_channels % 32 == 0:
+    if _plain_conv(module) and module.in_channels % 4 == 0 and module.out_channels % 4 == 0:
         return Conv2dTC(module)         # type: ignore[arg-type]
+    if type(module) is nn.Linear and module.in_features % 4 == 0 \
+            and module.out_features % 4 == 0:
+        return LinearTC(module)
     for name, child in list(module.named_children()):
         new = _convert_any(child)
         if new is not child:

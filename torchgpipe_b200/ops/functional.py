@@ -13,7 +13,7 @@ from torch import Tensor
 
 from torchgpipe_b200.ops import _lib
 
-__all__ = ['conv2d', 'conv2d_forward', 'instnorm_leaky', 'channel_moments', 'conv_supported',
+__all__ = ['linear', 'conv2d', 'conv2d_forward', 'instnorm_leaky', 'channel_moments', 'conv_supported',
            'refresh_dgrad_weight', 'batchnorm_act', 'maxpool2x2', 'upsample2x_cat']
 
 _CL = torch.channels_last
@@ -31,7 +31,7 @@ def conv_supported(c_in: int, c_out: int, stride, dilation, groups: int) -> bool
     stride = tuple(stride) if not isinstance(stride, int) else (stride, stride)
     dilation = tuple(dilation) if not isinstance(dilation, int) else (dilation, dilation)
     return (stride == (1, 1) and dilation == (1, 1) and groups == 1
-            and c_in % 4 == 0 and c_out % 32 == 0)
+            and c_in % 4 == 0 and c_out % 4 == 0)
 
 
 def conv2d_forward(x: Tensor, w: Tensor, padding: Tuple[int, int], stats_mode: int = 0,
@@ -370,3 +370,18 @@ class _UpsampleCat(torch.autograd.Function):
 def upsample2x_cat(x: Tensor, skip: Tensor) -> Tensor:
     """``cat(pad_to(upsample_nearest_x2(x), skip), skip, dim=1)`` in one pass (channels-last)."""
     return _UpsampleCat.apply(x, skip)
+
+
+def linear(x: Tensor, weight: Tensor, bias: Optional[Tensor] = None,
+           cache: Optional[dict] = None) -> Tensor:
+    """``F.linear`` on the tcgen05 convolution kernels: an ``[N, in]`` matrix is an NHWC image
+    batch with 1x1 pixels, the weight a 1x1 filter bank (forward, dgrad and wgrad all reuse the
+    convolution kernels). Needs ``in % 4 == 0`` and ``out % 4 == 0``."""
+    lead = x.shape[:-1]
+    x2 = x.reshape(-1, x.shape[-1])
+    y, _ = conv2d(x2.view(x2.size(0), x2.size(1), 1, 1), weight.view(*weight.shape, 1, 1),
+                  (0, 0), cache=cache)
+    y = y.view(x2.size(0), weight.size(0))
+    if bias is not None:
+        y = y + bias
+    return y.view(*lead, weight.size(0))

@@ -9,7 +9,7 @@ from torchgpipe_b200.checkpoint import is_recomputing
 from torchgpipe_b200.ops import functional as TF
 
 __all__ = ['Absorbed', 'ConvInstNormLeaky', 'Conv2dTC', 'ConvBatchNormAct', 'AbsorbedBatchNorm2d',
-           'MaxPool2x2', 'UpsamplePopCat']
+           'MaxPool2x2', 'UpsamplePopCat', 'LinearTC']
 
 _CL = torch.channels_last
 
@@ -269,3 +269,26 @@ def _make_upsample_popcat():
 
 
 UpsamplePopCat = _make_upsample_popcat()
+
+
+class LinearTC(nn.Module):
+    """``nn.Linear`` on the tcgen05 kernels (same ``weight`` / ``bias`` parameters and keys)."""
+
+    def __init__(self, linear: nn.Linear) -> None:
+        super().__init__()
+        self.in_features, self.out_features = linear.in_features, linear.out_features
+        self.weight, self.bias = linear.weight, linear.bias
+        self._cache: dict = {}
+
+    def refresh_derived_weights(self) -> None:
+        w4 = self.weight.view(self.out_features, self.in_features, 1, 1)
+        TF.refresh_dgrad_weight(w4, self._cache)
+
+    def extra_repr(self) -> str:
+        return (f'in_features={self.in_features}, out_features={self.out_features}, '
+                f'bias={self.bias is not None}, tcgen05/tf32')
+
+    def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
+        if input.is_cuda and input.dtype == torch.float32:
+            return TF.linear(input, self.weight, self.bias, cache=self._cache)
+        return F.linear(input, self.weight, self.bias)
