@@ -26,14 +26,10 @@ __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<floa
 // MODE 0: a = x,            out += (sum x, sum x^2)
 // MODE 1: a = dz, b = z:    dn = dz * (z > 0 ? 1 : slope); u = z > 0 ? z : z / slope
 //                           out += (sum dn, sum dn*u)            (norm+leaky backward reduction)
-// MODE 2: a = dz, b = z, BatchNorm+ReLU backward: dn = z > 0 ? dz : 0; needs x-hat which is not
-//         recoverable from a ReLU output, so the caller passes c = y (pre-norm) and per-channel
-//         mean / rstd:  out += (sum dn, sum dn * xhat)
 template <int MODE>
 __global__ void __launch_bounds__(kEwThreads)
 moments_kernel(const float* __restrict__ a, const float* __restrict__ b,
-               const float* __restrict__ mean, const float* __restrict__ rstd,
-               float* __restrict__ out, int P, int C, int slabs, float slope, int relu) {
+               float* __restrict__ out, int P, int C, int slabs, float slope) {
   // grid: (slabs, G). Thread t owns channel quad (t % Q) when Q divides the block size,
   // otherwise quads are re-derived per element.
   const int g = blockIdx.y;
@@ -52,11 +48,6 @@ moments_kernel(const float* __restrict__ a, const float* __restrict__ b,
     const int lanes_per_pixel = Q;
     const int pix_step = kEwThreads / lanes_per_pixel;
     float4 s1 = make_float4(0, 0, 0, 0), s2 = make_float4(0, 0, 0, 0);
-    float4 mu = make_float4(0, 0, 0, 0), rs = make_float4(0, 0, 0, 0);
-    if (MODE == 2) {
-      mu = ld4(mean + q * 4);
-      rs = ld4(rstd + q * 4);
-    }
     for (int p = p_begin + threadIdx.x / lanes_per_pixel; p < p_end; p += pix_step) {
       const size_t off = base + static_cast<size_t>(p) * C + q * 4;
       const float4 va = ld4(a + off);
@@ -75,18 +66,6 @@ moments_kernel(const float* __restrict__ a, const float* __restrict__ b,
   }
         TGB_ACC1(x) TGB_ACC1(y) TGB_ACC1(z) TGB_ACC1(w)
 #undef TGB_ACC1
-      } else {
-        const float4 vz = ld4(b + off);      // post-activation output (for the ReLU mask)
-        const float4 vy = ld4(mean == nullptr ? a + off : b + off);
-        (void)vy;
-#define TGB_ACC2(f)                                                       \
-  {                                                                       \
-    const float dn = (!relu || vz.f > 0.f) ? va.f : 0.f;                  \
-    s1.f += dn;                                                           \
-    s2.f = fmaf(dn, 0.f, s2.f);                                           \
-  }
-        TGB_ACC2(x) TGB_ACC2(y) TGB_ACC2(z) TGB_ACC2(w)
-#undef TGB_ACC2
       }
     }
     float* d = sh + q * 8;
@@ -354,7 +333,7 @@ extern "C" int tgb_moments(const float* x, float* out, int G, int P, int C,
   if (slabs < 1) slabs = 1;
   dim3 grid(slabs, G);
   moments_kernel<0><<<grid, kEwThreads, 2 * C * sizeof(float), stream>>>(
-      x, nullptr, nullptr, nullptr, out, P, C, slabs, 1.f, 0);
+      x, nullptr, out, P, C, slabs, 1.f);
   TGB_CHECK_LAUNCH("moments");
   return 0;
 }
@@ -367,7 +346,7 @@ extern "C" int tgb_in_leaky_bwd_sums(const float* dz, const float* z, float* out
   if (slabs < 1) slabs = 1;
   dim3 grid(slabs, G);
   moments_kernel<1><<<grid, kEwThreads, 2 * C * sizeof(float), stream>>>(
-      dz, z, nullptr, nullptr, out, P, C, slabs, slope, 0);
+      dz, z, out, P, C, slabs, slope);
   TGB_CHECK_LAUNCH("in_leaky_bwd_sums");
   return 0;
 }

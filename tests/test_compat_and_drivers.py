@@ -1,0 +1,60 @@
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+from torch import nn
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_compat_install_aliases_reference_import_paths():
+    code = (
+        'import sys; sys.path.insert(0, %r)\n'
+        'import torchgpipe_b200.compat as c; c.install()\n'
+        'import torchgpipe\n'
+        'from torchgpipe import GPipe, is_checkpointing, is_recomputing\n'
+        'from torchgpipe.balance import balance_by_time, balance_by_size, blockpartition\n'
+        'from torchgpipe.skip import skippable, stash, pop, Namespace, verify_skippables\n'
+        'from torchgpipe.batchnorm import DeferredBatchNorm\n'
+        'from torchgpipe.distributed import context\n'
+        'from torchgpipe.distributed.gpipe import DistributedGPipe, DistributedGPipeDataLoader\n'
+        'from torchgpipe.pipeline import clock_cycles\n'
+        'from torchgpipe.stream import CPUStream\n'
+        'import torchgpipe_b200\n'
+        'assert GPipe is torchgpipe_b200.GPipe\n'
+        'print("ok")\n' % ROOT)
+    out = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    assert out.stdout.strip().endswith('ok')
+
+
+def test_version_and_public_names():
+    import torchgpipe_b200
+    assert torchgpipe_b200.__version__
+    assert set(torchgpipe_b200.__all__) == {'GPipe', 'is_checkpointing', 'is_recomputing'}
+
+
+@pytest.mark.timeout(240)
+def test_speed_driver_smoke_on_cpu():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, 'benchmarks', 'speed.py'), 'unet',
+                          'pipeline-2', '--smoke', '--devices', 'cpu,cpu', '--steps', '1',
+                          '--warmup', '0'], capture_output=True, text=True, timeout=200,
+                         cwd=os.path.join(ROOT, 'benchmarks'))
+    assert out.returncode == 0, out.stderr[-2000:]
+    rec = json.loads(out.stdout.strip().splitlines()[-1])
+    assert rec['benchmark'] == 'unet-speed' and rec['samples_per_s'] > 0
+    assert sum(rec['balance']) == 241 and 'forward_bubble_frac' in rec
+
+
+def test_bench_reference_arm_reports_unavailable_without_install(tmp_path):
+    # run a copy of bench.py from a directory that has no baseline/_ref next to it
+    src = open(os.path.join(ROOT, 'bench.py')).read()
+    (tmp_path / 'bench.py').write_text(src)
+    out = subprocess.run([sys.executable, str(tmp_path / 'bench.py'), '--impl', 'reference'],
+                         capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    rec = json.loads(out.stdout.strip().splitlines()[-1])
+    assert rec['impl'] == 'reference' and 'unavailable' in rec
