@@ -58,8 +58,11 @@ def main():
 
     layout = HybridLayout(args.stages, args.replicas)
     B, C = (int(v) for v in args.model.split(','))
-    torch.manual_seed(0)            # identical initial weights in every replica
-    model = ops.convert_to_sm100(unet(depth=5, num_convs=B, base_channels=C))
+    # Built on the meta device: every rank materialises only its own stage (a 7.8 B-parameter
+    # model is 31 GB in fp32 - eight full host copies would not fit).
+    with torch.device('meta'):
+        model = unet(depth=5, num_convs=B, base_channels=C)
+    model = ops.convert_to_sm100(model)
     if args.balance:
         balance = [int(v) for v in args.balance.split(',')]
     elif (B, C, args.stages) == (24, 160, 4):
@@ -69,7 +72,13 @@ def main():
     hybrid = HybridPipeline(model, balance, args.chunks, layout, device,
                             checkpoint='except_last', cuda_graphs=not args.no_graphs,
                             use_symmetric=args.allreduce == 'fused')
-    opt = SGD(hybrid.model().parameters(), lr=0.1)
+    # identical initial weights in every replica: seed by stage, fan-in scaled normal
+    gen = torch.Generator(device=device).manual_seed(1234 + layout.stage)
+    with torch.no_grad():
+        for prm in hybrid.model().parameters():
+            fan_in = prm[0].numel() if prm.dim() > 1 else prm.numel()
+            prm.normal_(0.0, (2.0 / max(fan_in, 1)) ** 0.5, generator=gen)
+    opt = SGD(hybrid.model().parameters(), lr=0.01)
     first, last = layout.stage == 0, layout.stage == args.stages - 1
     torch.manual_seed(100 + layout.replica)     # different data per replica
     x = torch.rand(args.batch, 3, args.hw, args.hw, device=device) if first else None
@@ -107,11 +116,32 @@ def main():
     ms = t0.elapsed_time(t1) / args.steps
     ar_ms = sum(a.elapsed_time(b) for a, b in ar_events) / max(len(ar_events), 1)
     nbytes = hybrid.bucket.flat.numel() * 4
+    # library baseline on a bucket of the same size: NCCL all_reduce + scale, same group
+    nccl_ms = None
+    try:
+        scratch = torch.zeros_like(hybrid.bucket.flat)
+        for _ in range(2):
+            dist.all_reduce(scratch, group=layout.dp_group)
+            scratch.mul_(1.0 / args.replicas)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(3):
+            dist.all_reduce(scratch, group=layout.dp_group)
+            scratch.mul_(1.0 / args.replicas)
+        b.record()
+        torch.cuda.synchronize()
+        nccl_ms = a.elapsed_time(b) / 3
+        del scratch
+    except RuntimeError:
+        pass
     stats = torch.tensor([ms, ar_ms], device=device, dtype=torch.float64)
     dist.all_reduce(stats, op=dist.ReduceOp.MAX)
     gathered = [None] * dist.get_world_size()
     dist.all_gather_object(gathered, {'stage': layout.stage, 'replica': layout.replica,
-                                      'allreduce_ms': ar_ms, 'grad_bytes': nbytes})
+                                      'allreduce_ms': ar_ms, 'grad_bytes': nbytes,
+                                      'nccl_ms': nccl_ms,
+                                      'peak_gib': torch.cuda.max_memory_allocated() / 2 ** 30})
     if dist.get_rank() == 0:
         R = args.replicas
         per_stage = []
@@ -121,7 +151,11 @@ def main():
             wire = 2 * rows[0]['grad_bytes'] * (R - 1) / R
             ideal = wire / (LINK_GBS * 1e9) * 1e3
             per_stage.append({'stage': s, 'grad_mib': rows[0]['grad_bytes'] / 2 ** 20,
-                              'allreduce_ms': round(t, 3), 'roofline_ms': round(ideal, 3),
+                              'allreduce_ms': round(t, 3),
+                              'nccl_plus_scale_ms': (round(max(r['nccl_ms'] for r in rows), 3)
+                                                     if rows[0]['nccl_ms'] else None),
+                              'peak_gib': round(max(r['peak_gib'] for r in rows), 1),
+                              'roofline_ms': round(ideal, 3),
                               'fraction_of_roofline': round(ideal / t, 3) if t > 0 else None})
         print(json.dumps({'benchmark': 'ppdp', 'model': f'unet({B},{C})', 'stages': args.stages,
                           'replicas': R, 'balance': balance, 'allreduce': args.allreduce,

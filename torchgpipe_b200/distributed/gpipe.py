@@ -57,14 +57,23 @@ def get_module_partition(module: nn.Sequential,
                          device: Optional[torch.device],
                          ) -> nn.Sequential:
     """Returns stage ``rank`` of ``module`` under ``balance`` (children keep their names),
-    moved to ``device`` unless that is ``None``."""
+    moved to ``device`` unless that is ``None``.
+
+    A model built on the ``meta`` device (``with torch.device('meta'): model = ...``) is
+    materialised for this stage only: its parameters are allocated on ``device`` uninitialised
+    (``to_empty``) and the caller initialises or loads them. That is how a 7.8 B-parameter model
+    is set up with one process per GPU without every process building all of it in host memory.
+    """
     balance = list(balance)
     check_balance(module, balance)
     if not 0 <= rank < len(balance):
         raise RuntimeError('module and balance mismatch')
     partition = nn.Sequential(_stage_slices(module, balance)[rank])
     if device is not None:
-        partition.to(device)
+        if any(t.is_meta for t in list(partition.parameters()) + list(partition.buffers())):
+            partition.to_empty(device=device)
+        else:
+            partition.to(device)
     return partition
 
 
