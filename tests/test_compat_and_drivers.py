@@ -58,3 +58,40 @@ def test_bench_reference_arm_reports_unavailable_without_install(tmp_path):
     assert out.returncode == 0, out.stderr
     rec = json.loads(out.stdout.strip().splitlines()[-1])
     assert rec['impl'] == 'reference' and 'unavailable' in rec
+
+
+def test_demo_models_shapes_and_layer_counts():
+    # reference benchmarks/distributed/accuracy/{vgg,resnet}: 39-child VGG-16, 11-child ResNet
+    from torchgpipe_b200.models import resnet101_coarse, resnet50_coarse, vgg16
+    v, r101, r50 = vgg16(10), resnet101_coarse(10), resnet50_coarse(10)
+    assert len(v) == 39 and len(r101) == 11 and len(r50) == 11
+    assert sum(isinstance(m, nn.Conv2d) for m in v) == 13
+    assert sum(p.numel() for p in vgg16(1000).parameters()) == 138357544      # torchvision's vgg16
+    assert sum(p.numel() for p in resnet101_coarse(1000).parameters()) == 44549160
+    with torch.no_grad():
+        assert r50.eval()(torch.rand(2, 3, 64, 64)).shape == (2, 10)
+
+
+@pytest.mark.timeout(300)
+def test_distributed_accuracy_driver_two_ranks_on_gloo():
+    port = 29600 + os.getpid() % 300
+    out = subprocess.run(
+        [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2',
+         '--master-addr', '127.0.0.1', '--master-port', str(port),
+         os.path.join(ROOT, 'benchmarks', 'distributed_accuracy.py'), '--cpu', '--model',
+         'resnet50', '--balance', '5,6', '--batch-size', '4', '--chunks', '2', '--epochs', '1',
+         '--skip-epochs', '0', '--image-size', '32', '--synthetic', '--synthetic-size', '8',
+         '--lr', '0.001'], capture_output=True, text=True, timeout=280, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert 'valid accuracy' in out.stdout and 'samples/sec' in out.stdout
+
+
+@pytest.mark.timeout(240)
+def test_accuracy_driver_smoke_on_cpu():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, 'benchmarks', 'accuracy.py'),
+                          'gpipe-256', '--synthetic', '--epochs', '1', '--steps-per-epoch', '1',
+                          '--devices', 'cpu,cpu', '--batch', '4'], capture_output=True, text=True,
+                         timeout=200, cwd=os.path.join(ROOT, 'benchmarks'))
+    assert out.returncode == 0, out.stderr[-2000:]
+    rec = json.loads(out.stdout.strip().splitlines()[-1])
+    assert rec['experiment'] == 'gpipe-256' and rec['epoch'] == 1

@@ -600,6 +600,9 @@ class DistributedGPipeDataLoader:
     def _send_target(self, target: TensorOrTensors) -> None:
         if self._transport is not None and self._last_stage_rank is not None:
             tensors = (target,) if torch.is_tensor(target) else tuple(target)
+            device = getattr(self._transport, 'device', None)
+            if device is not None:      # NCCL moves device memory only; loaders yield host tensors
+                tensors = tuple(t.to(device, non_blocking=True) for t in tensors)
             self._transport.send(self._last_stage_rank, ('target', 0, 0), tensors)
         else:
             type(self)._put(self._last_stage_name, target)

@@ -5,5 +5,7 @@ from torchgpipe_b200.models.amoebanet import amoebanetd
 from torchgpipe_b200.models.resnet import resnet101
 from torchgpipe_b200.models.unet import unet
 from torchgpipe_b200.models.flatten import flatten_sequential
+from torchgpipe_b200.models.vgg import resnet50_coarse, resnet101_coarse, vgg16
 
-__all__ = ['amoebanetd', 'resnet101', 'unet', 'flatten_sequential']
+__all__ = ['amoebanetd', 'resnet101', 'unet', 'flatten_sequential', 'vgg16', 'resnet101_coarse',
+           'resnet50_coarse']
