@@ -133,6 +133,34 @@ int tgb_upsample2x_cat_fwd(const float* x, const float* skip, float* out, int N,
 int tgb_upsample2x_cat_bwd(const float* dout, float* dx, float* dskip, int N, int Hx, int Wx,
                            int C1, int Hs, int Ws, int C2, cudaStream_t stream);
 
+/* NHWC fp32 pooling family and residual joins (C multiple of 4; n multiple of 4).
+ * tgb_pool2d_fwd/bwd: k x k window, stride s, zero padding p (2p <= k), floor output size.
+ *   mode 0 max, 1 average over the valid (non-padding) pixels (count_include_pad=False),
+ *   2 average over k*k. Backward gathers over the covering windows (deterministic, no index
+ *   tensor; max routes to the first maximum in row-major window order like ATen) and needs x only
+ *   for mode 0. Reference call sites: nn.MaxPool2d(3,2,1) resnet/__init__.py:58, AvgPool2d /
+ *   MaxPool2d of amoebanet/operations.py:30-62.
+ * tgb_global_avgpool_fwd/bwd: y[N,C] = mean over HW of x[N,HW,C] (AdaptiveAvgPool2d(1)).
+ * tgb_add_act_fwd: z = relu?(a + b); tgb_relu_mask: d = dz where z > 0 else 0 (the gradient of
+ *   both summands; resnet/bottleneck.py:70-76 + the following nn.ReLU).
+ * tgb_bn_add_act_fwd: z = relu?(y * a[c] + b[c] + res) with coef from tgb_bn_prepare;
+ * tgb_bn_add_act_bwd: sums[C,2] (zero on entry) = (sum dn, sum dn*xhat), dn = dz masked by z > 0;
+ *   dy = a * (dn - S1/P - xhat*S2/P); dres = dn. (bn3 -> residual -> relu3 as one kernel.) */
+int tgb_pool2d_fwd(const float* x, float* y, int N, int H, int W, int C, int k, int s, int p,
+                   int mode, cudaStream_t stream);
+int tgb_pool2d_bwd(const float* x, const float* dy, float* dx, int N, int H, int W, int C, int k,
+                   int s, int p, int mode, cudaStream_t stream);
+int tgb_global_avgpool_fwd(const float* x, float* y, int N, int HW, int C, cudaStream_t stream);
+int tgb_global_avgpool_bwd(const float* dy, float* dx, int N, int HW, int C, cudaStream_t stream);
+int tgb_add_act_fwd(const float* a, const float* b, float* z, long long n, int relu,
+                    cudaStream_t stream);
+int tgb_relu_mask(const float* dz, const float* z, float* d, long long n, cudaStream_t stream);
+int tgb_bn_add_act_fwd(const float* y, const float* coef, const float* res, float* z, int P,
+                       int C, int relu, cudaStream_t stream);
+int tgb_bn_add_act_bwd(const float* dz, const float* y, const float* z, const float* coef,
+                       const float* saved, float* sums, float* dy, float* dres, int P, int C,
+                       int relu, cudaStream_t stream);
+
 /* Fused gradient all-reduce across data-parallel replicas: out = scale * sum over replicas, in
  * place in every replica's fp32 bucket, optionally also as a local bf16 copy. One kernel per
  * rank: barrier, reduce-scatter (P2P loads from the peers' buckets, or multimem.ld_reduce through

@@ -445,3 +445,126 @@ def test_linear_on_conv_kernels():
     assert rel_err(x.grad, xr.grad) < 2e-3
     assert rel_err(fused.weight.grad, plain.weight.grad) < 2e-3
     assert rel_err(fused.bias.grad, plain.bias.grad) < 1e-5
+
+
+POOL_CASES = [(3, 2, 1, 'max'), (3, 1, 1, 'max'), (2, 2, 0, 'max'), (2, 1, 0, 'max'),
+              (3, 1, 1, 'avg'), (3, 2, 1, 'avg'), (3, 1, 1, 'avg_include_pad'), (2, 2, 0, 'avg')]
+
+
+@pytest.mark.parametrize('k,s,p,mode', POOL_CASES)
+@pytest.mark.parametrize('shape', [(3, 64, 16, 16), (2, 36, 9, 7)])
+def test_pool2d_family_fwd_bwd(k, s, p, mode, shape):
+    from torchgpipe_b200.ops import functional as TF
+    torch.manual_seed(50)
+    x = torch.randn(*shape, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    xr = x.detach().clone().requires_grad_()
+    y = TF.pool2d(x, k, s, p, mode)
+    if mode == 'max':
+        yr = F.max_pool2d(xr, k, s, p)
+    else:
+        yr = F.avg_pool2d(xr, k, s, p, count_include_pad=mode == 'avg_include_pad')
+    assert y.shape == yr.shape
+    assert torch.allclose(y, yr, rtol=1e-6, atol=1e-6)
+    g = torch.randn_like(yr)
+    y.backward(g)
+    yr.backward(g)
+    assert torch.allclose(x.grad, xr.grad, rtol=1e-5, atol=1e-5)
+
+
+def test_max_pool_backward_routes_ties_like_aten():
+    from torchgpipe_b200.ops import functional as TF
+    x = torch.zeros(1, 4, 6, 6, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    xr = x.detach().clone().requires_grad_()
+    g = torch.arange(1., 37., device='cuda').view(1, 1, 6, 6).expand(1, 4, 6, 6)
+    TF.pool2d(x, 3, 1, 1, 'max').backward(g)
+    F.max_pool2d(xr, 3, 1, 1).backward(g)
+    assert torch.equal(x.grad, xr.grad)
+
+
+@pytest.mark.parametrize('shape', [(5, 2048, 7, 7), (3, 36, 5, 3), (2, 100, 1, 1)])
+def test_global_avgpool_fwd_bwd(shape):
+    from torchgpipe_b200.ops import functional as TF
+    torch.manual_seed(51)
+    x = torch.randn(*shape, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    xr = x.detach().clone().requires_grad_()
+    y, yr = TF.global_avgpool(x), F.adaptive_avg_pool2d(xr, 1)
+    assert y.shape == yr.shape and torch.allclose(y, yr, rtol=1e-5, atol=1e-6)
+    g = torch.randn_like(yr)
+    y.backward(g)
+    yr.backward(g)
+    assert torch.allclose(x.grad, xr.grad, rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize('relu', [False, True])
+def test_add_act_fwd_bwd(relu):
+    from torchgpipe_b200.ops import functional as TF
+    torch.manual_seed(52)
+    a = torch.randn(3, 36, 9, 7, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    b = torch.randn(3, 36, 9, 7, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    ar, br = a.detach().clone().requires_grad_(), b.detach().clone().requires_grad_()
+    z = TF.add_act(a, b, relu)
+    zr = F.relu(ar + br) if relu else ar + br
+    assert torch.equal(z, zr)
+    g = torch.randn_like(zr)
+    z.backward(g)
+    zr.backward(g)
+    assert torch.equal(a.grad, ar.grad) and torch.equal(b.grad, br.grad)
+
+
+@pytest.mark.parametrize('relu', [False, True])
+@pytest.mark.parametrize('C,H,W', [(256, 14, 14), (36, 7, 5), (2048, 4, 4)])
+def test_batchnorm_add_act_fwd_bwd(C, H, W, relu):
+    from torchgpipe_b200.ops import functional as TF
+    torch.manual_seed(53)
+    N = 6
+    y = (torch.randn(N, C, H, W, device='cuda') * 2 + 0.5).contiguous(memory_format=CL)
+    r = torch.randn(N, C, H, W, device='cuda').contiguous(memory_format=CL)
+    y.requires_grad_()
+    r.requires_grad_()
+    bn = nn.BatchNorm2d(C).cuda()
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5)
+        bn.bias.uniform_(-0.5, 0.5)
+    rm, rv = bn.running_mean.clone(), bn.running_var.clone()
+    w = bn.weight.detach().clone().requires_grad_()
+    b = bn.bias.detach().clone().requires_grad_()
+    z = TF.batchnorm_add_act(y, None, w, b, r, rm, rv, bn.eps, bn.momentum, relu)
+
+    yr, rr = y.detach().clone().requires_grad_(), r.detach().clone().requires_grad_()
+    zr = bn(yr) + rr
+    zr = F.relu(zr) if relu else zr
+    assert torch.allclose(z, zr, rtol=1e-4, atol=1e-4)
+    assert torch.allclose(rm, bn.running_mean, atol=1e-5)
+    assert torch.allclose(rv, bn.running_var, rtol=1e-4, atol=1e-5)
+
+    g = torch.randn_like(zr)
+    dy, dr, dw, db = torch.autograd.grad(z, (y, r, w, b), g)
+    dyr, drr, dwr, dbr = torch.autograd.grad(zr, (yr, rr, bn.weight, bn.bias), g)
+    assert rel_err(dy, dyr) < 1e-3 and rel_err(dr, drr) < 1e-5
+    assert rel_err(dw, dwr) < 1e-3 and rel_err(db, dbr) < 1e-3
+
+
+def test_converted_bottleneck_tail_is_one_fused_join():
+    """conv3, bn3, residual, relu3 -> deferring conv + BatchNormResidualAct; numerics vs plain."""
+    from torchgpipe_b200 import GPipe, ops
+    from torchgpipe_b200.models.resnet import bottleneck
+    torch.manual_seed(54)
+    proj = nn.Sequential(nn.Conv2d(64, 256, 1, bias=False), nn.BatchNorm2d(256))
+    plain = nn.Sequential(*bottleneck(64, 64, 1, proj).children(),
+                          *bottleneck(256, 64).children()).cuda()
+    fused = ops.convert_to_sm100(copy.deepcopy(plain))
+    names = [type(m).__name__ for m in fused]
+    assert names.count('BatchNormResidualAct') == 2 and 'Residual' not in names
+    assert list(fused.state_dict().keys()) == list(plain.state_dict().keys())
+    x = torch.randn(8, 64, 14, 14, device='cuda')
+    # through GPipe so that the skip route and checkpoint recomputation are exercised as well
+    gp = GPipe(plain, [22], devices=['cuda:0'], chunks=2, checkpoint='always')
+    gf = GPipe(fused, [22], devices=['cuda:0'], chunks=2, checkpoint='always')
+    out, ref = gf(x), gp(x)
+    assert rel_err(out, ref) < 5e-3
+    out.square().mean().backward()
+    ref.square().mean().backward()
+    for (n, p), (_, q) in zip(gf.named_parameters(), gp.named_parameters()):
+        assert rel_err(p.grad, q.grad) < 3e-2, n
+    for (n, p), (_, q) in zip(gf.named_buffers(), gp.named_buffers()):
+        assert torch.allclose(p.float(), q.float(), rtol=1e-3, atol=1e-3), n

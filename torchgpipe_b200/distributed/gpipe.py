@@ -32,7 +32,7 @@ from torchgpipe_b200.distributed import context
 from torchgpipe_b200.distributed.transport import ChannelTransport, Transport
 from torchgpipe_b200.distributed.utils import to
 from torchgpipe_b200.gpipe import (BalanceError, check_balance, recommend_auto_balance,
-                                   verify_module)
+                                   verify_fusion_partners, verify_module)
 from torchgpipe_b200.microbatch import Batch
 from torchgpipe_b200.skip.layout import inspect_skip_layout
 from torchgpipe_b200.skip.namespace import Namespace
@@ -69,6 +69,7 @@ def get_module_partition(module: nn.Sequential,
     if not 0 <= rank < len(balance):
         raise RuntimeError('module and balance mismatch')
     partition = nn.Sequential(_stage_slices(module, balance)[rank])
+    verify_fusion_partners(partition, rank)
     if device is not None:
         if any(t.is_meta for t in list(partition.parameters()) + list(partition.buffers())):
             partition.to_empty(device=device)

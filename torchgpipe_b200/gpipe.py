@@ -97,10 +97,30 @@ def split_module(module: nn.Sequential,
     stages = []
     for j, count in enumerate(balance):
         stage = nn.Sequential(OrderedDict(next(named) for _ in range(count)))
+        verify_fusion_partners(stage, j)
         stage.to(devices[j])
         stages.append(stage)
 
     return nn.ModuleList(stages), balance, devices[:len(balance)]
+
+
+def verify_fusion_partners(stage: nn.Module, index: int) -> None:
+    """A fused layer made by ``ops.convert_to_sm100`` may use the parameters of a neighbouring
+    placeholder layer (``fusion_partners()``); both must land in the same stage."""
+    members = None
+    for name, layer in stage.named_modules():
+        partners = getattr(layer, 'fusion_partners', None)
+        if partners is None:
+            continue
+        if members is None:
+            members = {id(m) for m in stage.modules()}
+        for partner in partners():
+            if id(partner) not in members:
+                raise ValueError(
+                    f'balance cuts a fused run: layer {name!r} of stage {index} uses the '
+                    f'parameters of a {type(partner).__name__} layer placed in another stage; '
+                    'move the cut by one layer or convert the model after choosing the balance '
+                    'with that run left unfused')
 
 
 _MOVING_DENIED = ('denied to move parameters and buffers, '

@@ -11,9 +11,10 @@ from typing import List, Tuple
 
 from torch import nn
 
-from torchgpipe_b200.ops.modules import (Absorbed, AbsorbedBatchNorm2d, Conv2dTC,
-                                         ConvBatchNormAct, ConvInstNormLeaky, LinearTC,
-                                         MaxPool2x2, UpsamplePopCat)
+from torchgpipe_b200.ops.modules import (Absorbed, AbsorbedBatchNorm2d, BatchNormResidualAct,
+                                         Conv2dTC, ConvBatchNormAct, ConvInstNormLeaky,
+                                         GlobalAvgPoolNHWC, LinearTC, MaxPool2x2, Pool2dNHWC,
+                                         UpsamplePopCat)
 
 __all__ = ['convert_to_sm100']
 
@@ -71,6 +72,48 @@ def _match_upsample_popcat(layers: List[Tuple[str, nn.Module]], i: int) -> bool:
             and nxt.poppable_names == frozenset(['skip']) and not nxt.stashable_names)
 
 
+def _is_residual(m: nn.Module) -> bool:
+    """The sequential ResNet's ``Residual`` skippable: pops ``identity``, optionally projects it
+    with ``downsample`` and adds it to the input."""
+    from torchgpipe_b200.skip.skippable import Skippable
+    return (isinstance(m, Skippable) and type(m.module).__name__ == 'Residual'
+            and m.poppable_names == frozenset(['identity']) and not m.stashable_names
+            and hasattr(m.module, 'downsample'))
+
+
+def _square(v) -> int:
+    """The common value of an int-or-pair argument, -1 if the pair is not square."""
+    if isinstance(v, (tuple, list)):
+        return int(v[0]) if len(v) == 2 and v[0] == v[1] else -1
+    return int(v)
+
+
+def _convert_pool(m: nn.Module):
+    """NHWC kernel front-end for a pooling layer, or ``None`` if it is not covered."""
+    if type(m) is nn.MaxPool2d:
+        k, s, p = _square(m.kernel_size), _square(m.stride or m.kernel_size), _square(m.padding)
+        if (min(k, s) >= 1 and 0 <= p and 2 * p <= k <= 7 and _square(m.dilation) == 1
+                and not m.ceil_mode and not m.return_indices):
+            return Pool2dNHWC(k, s, p, 'max')
+    if type(m) is nn.AvgPool2d:
+        k, s, p = _square(m.kernel_size), _square(m.stride or m.kernel_size), _square(m.padding)
+        if (min(k, s) >= 1 and 0 <= p and 2 * p <= k <= 7 and not m.ceil_mode
+                and m.divisor_override is None):
+            return Pool2dNHWC(k, s, p, 'avg_include_pad' if m.count_include_pad else 'avg')
+    if type(m) is nn.AdaptiveAvgPool2d and m.output_size in (1, (1, 1)):
+        return GlobalAvgPoolNHWC()
+    return None
+
+
+def _fused_residual(residual: nn.Module, bn, relu: bool) -> nn.Module:
+    downsample = residual.module.downsample
+    if downsample is not None:
+        downsample = _convert_any(downsample)
+    fused = BatchNormResidualAct(bn, downsample, relu)
+    fused.namespaces = dict(residual.namespaces)        # same skip route as the original
+    return fused
+
+
 def _convert_sequential(module: nn.Sequential) -> nn.Sequential:
     layers = list(module.named_children())
     out: 'OrderedDict[str, nn.Module]' = OrderedDict()
@@ -97,6 +140,25 @@ def _convert_sequential(module: nn.Sequential) -> nn.Sequential:
             i += 1
             continue
         n = _match_conv_bn(layers, i)
+        if n == 2 and i + 2 < len(layers) and _is_residual(layers[i + 2][1]):
+            # conv, bn, residual [, relu]: the normalisation moves into the residual join
+            conv, bn, residual = (layers[i + k][1] for k in range(3))
+            relu = i + 3 < len(layers) and type(layers[i + 3][1]) is nn.ReLU
+            bn.__class__ = AbsorbedBatchNorm2d
+            out[name] = ConvBatchNormAct(conv, bn, relu=False, defer=True)
+            out[layers[i + 1][0]] = bn
+            out[layers[i + 2][0]] = _fused_residual(residual, bn, relu)
+            if relu:
+                out[layers[i + 3][0]] = Absorbed(layers[i + 3][1], into=layers[i + 2][0])
+            i += 4 if relu else 3
+            continue
+        if _is_residual(layer):
+            relu = i + 1 < len(layers) and type(layers[i + 1][1]) is nn.ReLU
+            out[name] = _fused_residual(layer, None, relu)
+            if relu:
+                out[layers[i + 1][0]] = Absorbed(layers[i + 1][1], into=name)
+            i += 2 if relu else 1
+            continue
         if n:
             conv, bn = layers[i][1], layers[i + 1][1]
             bn.__class__ = AbsorbedBatchNorm2d      # same object: parameters, buffers, keys stay
@@ -116,10 +178,14 @@ def _convert_sequential(module: nn.Sequential) -> nn.Sequential:
 def _convert_any(module: nn.Module) -> nn.Module:
     """Recursive rewrite of an arbitrary module tree (names of all children are preserved)."""
     if isinstance(module, (ConvInstNormLeaky, ConvBatchNormAct, Conv2dTC, Absorbed,
-                           AbsorbedBatchNorm2d, MaxPool2x2, UpsamplePopCat, LinearTC)):
+                           AbsorbedBatchNorm2d, MaxPool2x2, UpsamplePopCat, LinearTC, Pool2dNHWC,
+                           GlobalAvgPoolNHWC, BatchNormResidualAct)):
         return module
     if type(module) is nn.Sequential:
         return _convert_sequential(module)
+    pool = _convert_pool(module)
+    if pool is not None:
+        return pool
     if _plain_conv(module) and module.in_channels % 4 == 0 and module.out_channels % 4 == 0:
         return Conv2dTC(module)         # type: ignore[arg-type]
     if type(module) is nn.Linear and module.in_features % 4 == 0 \
@@ -137,7 +203,9 @@ def convert_to_sm100(module: nn.Module) -> nn.Module:
 
     Recognised runs inside every (nested) ``nn.Sequential``:
     ``Conv2d, Dropout2d, InstanceNorm2d, LeakyReLU`` (U-Net cell) and ``Conv2d, BatchNorm2d
-    [, ReLU]`` (ResNet / AmoebaNet); any other stride-1 convolution with suitable channel counts
+    [, ReLU]`` (ResNet / AmoebaNet), ``Conv2d, BatchNorm2d, Residual [, ReLU]`` (the tail of a
+    sequential bottleneck: normalisation, shortcut add and ReLU in one kernel), max / average /
+    global-average pooling; any other stride-1 convolution with suitable channel counts
     becomes a :class:`Conv2dTC`. Number, order and names of layers and parameters never change.
     """
     return _convert_any(module)

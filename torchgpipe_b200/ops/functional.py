@@ -14,7 +14,8 @@ from torch import Tensor
 from torchgpipe_b200.ops import _lib
 
 __all__ = ['linear', 'conv2d', 'conv2d_forward', 'instnorm_leaky', 'channel_moments', 'conv_supported',
-           'refresh_dgrad_weight', 'batchnorm_act', 'maxpool2x2', 'upsample2x_cat']
+           'refresh_dgrad_weight', 'batchnorm_act', 'maxpool2x2', 'upsample2x_cat', 'pool2d',
+           'pool_supported', 'global_avgpool', 'add_act', 'batchnorm_add_act']
 
 _CL = torch.channels_last
 _c_int = ctypes.c_int
@@ -385,3 +386,186 @@ def linear(x: Tensor, weight: Tensor, bias: Optional[Tensor] = None,
     if bias is not None:
         y = y + bias
     return y.view(*lead, weight.size(0))
+
+
+# ---------------------------------------------------------------- pooling family / residual joins
+_POOL_MODES = {'max': 0, 'avg': 1, 'avg_include_pad': 2}
+
+
+class _Pool2d(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: Tensor, k: int, s: int, p: int, mode: int):  # type: ignore[override]
+        lib = _lib.require()
+        x = _cl(x)
+        N, C, H, W = x.shape
+        Ho, Wo = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
+        y = torch.empty((N, C, Ho, Wo), device=x.device, dtype=torch.float32, memory_format=_CL)
+        with torch.cuda.device(x.device):
+            rc = lib.tgb_pool2d_fwd(_lib.ptr(x), _lib.ptr(y), _c_int(N), _c_int(H), _c_int(W),
+                                    _c_int(C), _c_int(k), _c_int(s), _c_int(p), _c_int(mode),
+                                    _lib.stream_ptr(x.device))
+        _lib.check(rc, 'tgb_pool2d_fwd')
+        ctx.geom = (N, C, H, W, k, s, p, mode)
+        if mode == 0:
+            ctx.save_for_backward(x)        # average pooling needs no input in backward
+        return y
+
+    @staticmethod
+    def backward(ctx, dy: Tensor):  # type: ignore[override]
+        lib = _lib.require()
+        N, C, H, W, k, s, p, mode = ctx.geom
+        x = ctx.saved_tensors[0] if mode == 0 else None
+        dy = _cl(dy)
+        dx = torch.empty((N, C, H, W), device=dy.device, dtype=torch.float32, memory_format=_CL)
+        with torch.cuda.device(dy.device):
+            rc = lib.tgb_pool2d_bwd(_lib.ptr(x), _lib.ptr(dy), _lib.ptr(dx), _c_int(N), _c_int(H),
+                                    _c_int(W), _c_int(C), _c_int(k), _c_int(s), _c_int(p),
+                                    _c_int(mode), _lib.stream_ptr(dy.device))
+        _lib.check(rc, 'tgb_pool2d_bwd')
+        return dx, None, None, None, None
+
+
+def pool2d(x: Tensor, kernel_size: int, stride: int, padding: int = 0, mode: str = 'max') -> Tensor:
+    """``MaxPool2d`` / ``AvgPool2d`` (square window, floor output size) on a channels-last fp32
+    CUDA tensor with ``C % 4 == 0``. ``mode``: ``'max'``, ``'avg'`` (count_include_pad=False) or
+    ``'avg_include_pad'``."""
+    return _Pool2d.apply(x, int(kernel_size), int(stride), int(padding), _POOL_MODES[mode])
+
+
+def pool_supported(x: Tensor, kernel_size: int, padding: int) -> bool:
+    return (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.size(1) % 4 == 0
+            and 1 <= kernel_size <= 7 and 2 * padding <= kernel_size)
+
+
+class _GlobalAvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: Tensor):  # type: ignore[override]
+        lib = _lib.require()
+        x = _cl(x)
+        N, C, H, W = x.shape
+        y = torch.empty((N, C, 1, 1), device=x.device, dtype=torch.float32, memory_format=_CL)
+        with torch.cuda.device(x.device):
+            rc = lib.tgb_global_avgpool_fwd(_lib.ptr(x), _lib.ptr(y), _c_int(N), _c_int(H * W),
+                                            _c_int(C), _lib.stream_ptr(x.device))
+        _lib.check(rc, 'tgb_global_avgpool_fwd')
+        ctx.geom = (N, C, H, W)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy: Tensor):  # type: ignore[override]
+        lib = _lib.require()
+        N, C, H, W = ctx.geom
+        dy = dy.reshape(N, C).contiguous()
+        dx = torch.empty((N, C, H, W), device=dy.device, dtype=torch.float32, memory_format=_CL)
+        with torch.cuda.device(dy.device):
+            rc = lib.tgb_global_avgpool_bwd(_lib.ptr(dy), _lib.ptr(dx), _c_int(N), _c_int(H * W),
+                                            _c_int(C), _lib.stream_ptr(dy.device))
+        _lib.check(rc, 'tgb_global_avgpool_bwd')
+        return dx
+
+
+def global_avgpool(x: Tensor) -> Tensor:
+    """``AdaptiveAvgPool2d(1)``: ``[N,C,H,W]`` (channels-last fp32, C % 4 == 0) -> ``[N,C,1,1]``."""
+    return _GlobalAvgPool.apply(x)
+
+
+class _AddAct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a: Tensor, b: Tensor, relu: bool):  # type: ignore[override]
+        lib = _lib.require()
+        a, b = _cl(a), _cl(b)
+        z = torch.empty_like(a, memory_format=_CL)
+        with torch.cuda.device(a.device):
+            rc = lib.tgb_add_act_fwd(_lib.ptr(a), _lib.ptr(b), _lib.ptr(z), _c_ll(a.numel()),
+                                     _c_int(int(relu)), _lib.stream_ptr(a.device))
+        _lib.check(rc, 'tgb_add_act_fwd')
+        ctx.relu = relu
+        if relu:
+            ctx.save_for_backward(z)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz: Tensor):  # type: ignore[override]
+        if not ctx.relu:
+            return dz, dz, None
+        lib = _lib.require()
+        z, = ctx.saved_tensors
+        dz = _cl(dz)
+        d = torch.empty_like(z, memory_format=_CL)
+        with torch.cuda.device(z.device):
+            rc = lib.tgb_relu_mask(_lib.ptr(dz), _lib.ptr(z), _lib.ptr(d), _c_ll(z.numel()),
+                                   _lib.stream_ptr(z.device))
+        _lib.check(rc, 'tgb_relu_mask')
+        return d, d, None
+
+
+def add_act(a: Tensor, b: Tensor, relu: bool = True) -> Tensor:
+    """``relu?(a + b)`` for two same-shape channels-last fp32 CUDA tensors (numel % 4 == 0); the
+    backward is one masked copy shared by both summands."""
+    return _AddAct.apply(a, b, bool(relu))
+
+
+class _BatchNormAddAct(torch.autograd.Function):
+    """z = relu?(BatchNorm(y) + res), training mode, statistics given as per-channel
+    (sum, sum of squares). Saves ``y``, ``z`` (alive anyway as the next layer's input) and two
+    ``[C,2]`` tables; the ReLU mask comes from ``z > 0``."""
+
+    @staticmethod
+    def forward(ctx, y: Tensor, stats: Tensor, weight: Optional[Tensor],  # type: ignore[override]
+                bias: Optional[Tensor], res: Tensor, running_mean: Optional[Tensor],
+                running_var: Optional[Tensor], eps: float, momentum: float, relu: bool):
+        lib = _lib.require()
+        y, res = _cl(y), _cl(res)
+        N, C, H, W = y.shape
+        P = N * H * W
+        coef = torch.empty((C, 2), device=y.device, dtype=torch.float32)
+        saved = torch.empty((C, 2), device=y.device, dtype=torch.float32)
+        z = torch.empty_like(y, memory_format=_CL)
+        with torch.cuda.device(y.device):
+            st = _lib.stream_ptr(y.device)
+            rc = lib.tgb_bn_prepare(_lib.ptr(stats), _lib.ptr(weight), _lib.ptr(bias),
+                                    _lib.ptr(coef), _lib.ptr(saved), _lib.ptr(running_mean),
+                                    _lib.ptr(running_var), _c_int(P), _c_int(C), _c_float(eps),
+                                    _c_float(momentum), st)
+            _lib.check(rc, 'tgb_bn_prepare')
+            rc = lib.tgb_bn_add_act_fwd(_lib.ptr(y), _lib.ptr(coef), _lib.ptr(res), _lib.ptr(z),
+                                        _c_int(P), _c_int(C), _c_int(int(relu)), st)
+            _lib.check(rc, 'tgb_bn_add_act_fwd')
+        ctx.save_for_backward(y, z, coef, saved)
+        ctx.relu = relu
+        ctx.affine = (weight is not None, bias is not None)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz: Tensor):  # type: ignore[override]
+        lib = _lib.require()
+        y, z, coef, saved = ctx.saved_tensors
+        dz = _cl(dz)
+        N, C, H, W = y.shape
+        P = N * H * W
+        sums = torch.zeros((C, 2), device=y.device, dtype=torch.float32)
+        dy = torch.empty_like(y, memory_format=_CL)
+        dres = torch.empty_like(y, memory_format=_CL)
+        with torch.cuda.device(y.device):
+            rc = lib.tgb_bn_add_act_bwd(_lib.ptr(dz), _lib.ptr(y), _lib.ptr(z), _lib.ptr(coef),
+                                        _lib.ptr(saved), _lib.ptr(sums), _lib.ptr(dy),
+                                        _lib.ptr(dres), _c_int(P), _c_int(C),
+                                        _c_int(int(ctx.relu)), _lib.stream_ptr(y.device))
+        _lib.check(rc, 'tgb_bn_add_act_bwd')
+        dweight = sums[:, 1].clone() if ctx.affine[0] else None
+        dbias = sums[:, 0].clone() if ctx.affine[1] else None
+        return dy, None, dweight, dbias, dres, None, None, None, None, None
+
+
+def batchnorm_add_act(y: Tensor, stats: Optional[Tensor], weight: Optional[Tensor],
+                      bias: Optional[Tensor], res: Tensor,
+                      running_mean: Optional[Tensor] = None,
+                      running_var: Optional[Tensor] = None, eps: float = 1e-5,
+                      momentum: float = 0.1, relu: bool = True) -> Tensor:
+    """Fused training-mode ``ReLU?(BatchNorm2d(y) + res)`` (``bn3 -> residual -> relu3`` of a
+    bottleneck, reference ``benchmarks/models/resnet/bottleneck.py:31-79``). Arguments as
+    :func:`batchnorm_act`."""
+    if stats is None or stats.numel() == 0:
+        stats = channel_moments(y)
+    return _BatchNormAddAct.apply(y, stats, weight, bias, res, running_mean, running_var,
+                                  float(eps), float(momentum), bool(relu))

@@ -9,7 +9,8 @@ from torchgpipe_b200.checkpoint import is_recomputing
 from torchgpipe_b200.ops import functional as TF
 
 __all__ = ['Absorbed', 'ConvInstNormLeaky', 'Conv2dTC', 'ConvBatchNormAct', 'AbsorbedBatchNorm2d',
-           'MaxPool2x2', 'UpsamplePopCat', 'LinearTC']
+           'MaxPool2x2', 'UpsamplePopCat', 'LinearTC', 'Pool2dNHWC', 'GlobalAvgPoolNHWC',
+           'BatchNormResidualAct']
 
 _CL = torch.channels_last
 
@@ -164,6 +165,32 @@ class AbsorbedBatchNorm2d(nn.BatchNorm2d):
                 self.counter = self.tracked = 0
 
 
+def _bn_running_args(bn: AbsorbedBatchNorm2d, stats: Tensor, count: int):
+    """What the fused kernels need to keep ``bn``'s running estimates: ``(running_mean,
+    running_var, momentum)`` - ``(None, None, 0)`` while recomputing, without tracking, or under
+    DeferredBatchNorm (whose accumulation happens here as a side effect)."""
+    if bn.track_running_stats and not is_recomputing():
+        if bn.deferred_chunks:
+            bn.track(stats, count)
+        else:
+            bn.num_batches_tracked += 1
+            momentum = (1.0 / float(bn.num_batches_tracked) if bn.momentum is None
+                        else bn.momentum)
+            return bn.running_mean, bn.running_var, momentum
+    return None, None, 0.0
+
+
+def _bn_torch(bn: AbsorbedBatchNorm2d, y: Tensor) -> Tensor:
+    """ATen path (CPU tensors, eval mode, other dtypes) with the same bookkeeping."""
+    if bn.training and (is_recomputing() or bn.deferred_chunks):
+        if bn.deferred_chunks and bn.track_running_stats and not is_recomputing():
+            with torch.no_grad():
+                stats = torch.stack([y.sum((0, 2, 3)), (y * y).sum((0, 2, 3))], dim=1)
+            bn.track(stats, y.numel() // y.size(1))
+        return F.batch_norm(y, None, None, bn.weight, bn.bias, True, 0.0, bn.eps)
+    return nn.BatchNorm2d.forward(bn, y)
+
+
 class ConvBatchNormAct(nn.Module):
     """``Conv2d(bias=False) -> BatchNorm2d [-> ReLU]`` with the statistics taken in the
     convolution's epilogue and one normalise(+ReLU) pass (reference: separate cuDNN conv, BN and
@@ -173,8 +200,12 @@ class ConvBatchNormAct(nn.Module):
     parameters and running statistics; this module only *uses* them.
     """
 
-    def __init__(self, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool) -> None:
+    def __init__(self, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool,
+                 defer: bool = False) -> None:
         super().__init__()
+        # defer=True: output (raw convolution, statistics) and leave the normalisation to a
+        # following BatchNormResidualAct, which fuses it with the shortcut add and the ReLU
+        self.defer = bool(defer)
         self.in_channels, self.out_channels = conv.in_channels, conv.out_channels
         self.kernel_size, self.padding, self.stride = conv.kernel_size, conv.padding, conv.stride
         self.weight = conv.weight
@@ -193,18 +224,22 @@ class ConvBatchNormAct(nn.Module):
     def extra_repr(self) -> str:
         return (f'{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, '
                 f'stride={self.stride}, padding={self.padding}, bn(eps={self.bn.eps}), '
-                f'relu={self.relu}, tcgen05/tf32')
+                f'relu={self.relu}, defer={self.defer}, tcgen05/tf32')
 
-    def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
+    def fusion_partners(self):
+        # a deferring layer only hands (convolution, statistics) on: it may sit in another stage
+        return [] if self.defer else [self.bn]
+
+    def forward(self, input: Tensor):  # type: ignore[override]
         bn = self.bn
         native = (input.is_cuda and input.dtype == torch.float32
                   and self.out_channels % 4 == 0)
-        if not native or not bn.training:
+        training = self.training if self.defer else bn.training
+        if not native or not training:
             y = F.conv2d(input, self.weight, None, self.stride, self.padding)
-            use_batch_stats = bn.training or bn.running_mean is None
-            y = F.batch_norm(y, None if use_batch_stats else bn.running_mean,
-                             None if use_batch_stats else bn.running_var, bn.weight, bn.bias,
-                             use_batch_stats, 0.0, bn.eps)
+            if self.defer:
+                return y, y.new_empty(0)
+            y = _bn_torch(bn, y)
             return F.relu(y) if self.relu else y
 
         if self.stride == (1, 1) and TF.conv_supported(self.in_channels, self.out_channels,
@@ -216,18 +251,11 @@ class ConvBatchNormAct(nn.Module):
             x = input.contiguous(memory_format=_CL)
             y = F.conv2d(x, self.weight, None, self.stride, self.padding)
             stats = TF.channel_moments(y)
+        if self.defer:
+            return y, stats
 
-        running_mean = running_var = None
-        momentum = 0.0
-        recomputing = is_recomputing()
-        if bn.track_running_stats and not recomputing:
-            if bn.deferred_chunks:
-                bn.track(stats, y.numel() // y.size(1))
-            else:
-                bn.num_batches_tracked += 1
-                momentum = (1.0 / float(bn.num_batches_tracked) if bn.momentum is None
-                            else bn.momentum)
-                running_mean, running_var = bn.running_mean, bn.running_var
+        running_mean, running_var, momentum = _bn_running_args(bn, stats,
+                                                               y.numel() // y.size(1))
         return TF.batchnorm_act(y, stats, bn.weight, bn.bias, running_mean, running_var, bn.eps,
                                 momentum, self.relu)
 
@@ -269,6 +297,97 @@ def _make_upsample_popcat():
 
 
 UpsamplePopCat = _make_upsample_popcat()
+
+
+class Pool2dNHWC(nn.Module):
+    """``nn.MaxPool2d`` / ``nn.AvgPool2d`` (square window, floor mode) on the NHWC kernels with an
+    index-free, deterministic backward. ``mode``: ``'max'``, ``'avg'`` (count_include_pad=False)
+    or ``'avg_include_pad'``."""
+
+    def __init__(self, kernel_size: int, stride: int, padding: int, mode: str) -> None:
+        super().__init__()
+        self.kernel_size, self.stride, self.padding, self.mode = kernel_size, stride, padding, mode
+
+    def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
+        if TF.pool_supported(input, self.kernel_size, self.padding):
+            return TF.pool2d(input, self.kernel_size, self.stride, self.padding, self.mode)
+        if self.mode == 'max':
+            return F.max_pool2d(input, self.kernel_size, self.stride, self.padding)
+        return F.avg_pool2d(input, self.kernel_size, self.stride, self.padding,
+                            count_include_pad=self.mode == 'avg_include_pad')
+
+    def extra_repr(self) -> str:
+        return (f'kernel_size={self.kernel_size}, stride={self.stride}, padding={self.padding}, '
+                f'mode={self.mode}, nhwc')
+
+
+class GlobalAvgPoolNHWC(nn.Module):
+    """``nn.AdaptiveAvgPool2d(1)`` on the NHWC kernel."""
+
+    def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
+        if (input.is_cuda and input.dtype == torch.float32 and input.dim() == 4
+                and input.size(1) % 4 == 0):
+            return TF.global_avgpool(input)
+        return F.adaptive_avg_pool2d(input, 1)
+
+
+def _make_residual():
+    from torchgpipe_b200.skip import pop, skippable
+
+    @skippable(pop=['identity'])
+    class BatchNormResidualAct(nn.Module):
+        """``bn3 -> residual (pop shortcut, optional projection, add) -> relu3`` of a bottleneck
+        (reference ``benchmarks/models/resnet/bottleneck.py:31-79``) as one kernel each way.
+
+        Sits at the position of the reference's ``Residual`` layer (same skip route, same
+        ``downsample`` child and keys). Its input is the ``(raw convolution, statistics)`` pair a
+        deferring :class:`ConvBatchNormAct` produced; the BatchNorm layer in between is an
+        :class:`AbsorbedBatchNorm2d` whose parameters this layer uses. Without a BatchNorm partner
+        (``bn=None``) it is the plain fused ``relu?(input + shortcut)``.
+        """
+
+        def __init__(self, bn: Optional[nn.BatchNorm2d], downsample: Optional[nn.Module],
+                     relu: bool) -> None:
+            super().__init__()
+            self._bn = (bn,)
+            self.downsample = downsample
+            self.relu = bool(relu)
+
+        @property
+        def bn(self) -> Optional[AbsorbedBatchNorm2d]:
+            return self._bn[0]  # type: ignore[return-value]
+
+        def fusion_partners(self):
+            return [] if self.bn is None else [self.bn]
+
+        def extra_repr(self) -> str:
+            return f'bn={"absorbed" if self.bn is not None else None}, relu={self.relu}'
+
+        def forward(self, input):  # type: ignore[override]
+            identity = yield pop('identity')
+            if self.downsample is not None:
+                identity = self.downsample(identity)
+            bn = self.bn
+            if bn is None:
+                y = input
+                if (y.is_cuda and y.dtype == torch.float32 and y.dim() == 4
+                        and y.size(1) % 4 == 0):
+                    return TF.add_act(y, identity, self.relu)
+                y = y + identity
+                return F.relu(y) if self.relu else y
+            y, stats = input
+            if stats.numel() == 0 or not bn.training:       # ATen path (CPU / eval)
+                z = _bn_torch(bn, y) + identity
+                return F.relu(z) if self.relu else z
+            running_mean, running_var, momentum = _bn_running_args(bn, stats,
+                                                                   y.numel() // y.size(1))
+            return TF.batchnorm_add_act(y, stats, bn.weight, bn.bias, identity, running_mean,
+                                        running_var, bn.eps, momentum, self.relu)
+
+    return BatchNormResidualAct
+
+
+BatchNormResidualAct = _make_residual()
 
 
 class LinearTC(nn.Module):
