@@ -2,7 +2,9 @@
 # compute-sanitizer pass over the stand-alone kernel self-test (the reference has no
 # sanitizer runs; the hand-written kernels here get memcheck / synccheck / initcheck / racecheck).
 # Usage (on a GPU box): tools/sanitize.sh [out-file]      - needs `make -C csrc` first.
-# Each case is bounded by `timeout`; a tool that cannot instrument a kernel is reported, not fatal.
+# NOTE: on the shared B200 pool of this build compute-sanitizer is administratively closed (the
+# gpurun wrapper refuses it), so no summary is committed under profiles/; the script is for boxes
+# where the tool may run. Each case is bounded by `timeout`; a tool that cannot instrument a kernel is reported, not fatal.
 out=${1:-gpurun_out/sanitizer_summary.txt}
 mkdir -p "$(dirname "$out")"
 : > "$out"
