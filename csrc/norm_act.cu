@@ -11,6 +11,7 @@
 // BatchNorm with P = N*H*W), C % 4 == 0.
 #include <cuda_runtime.h>
 #include <cstdint>
+#include "bn_reduce.cuh"
 #include "tgb_internal.h"
 
 namespace tgb {
@@ -226,57 +227,7 @@ bn_apply_kernel(const float* __restrict__ y, const float* __restrict__ coef,
   }
 }
 
-// sums[c] += (sum dn, sum dn * xhat); dn = dz masked by the ReLU (re-derived from y), xhat from y
-__global__ void __launch_bounds__(kEwThreads)
-bn_bwd_reduce_kernel(const float* __restrict__ dz, const float* __restrict__ y,
-                     const float* __restrict__ coef, const float* __restrict__ saved,
-                     float* __restrict__ sums, int P, int C, int slabs, int relu) {
-  const int Q = C >> 2;
-  const int pix_per_slab = (P + slabs - 1) / slabs;
-  const int p_begin = blockIdx.x * pix_per_slab;
-  const int p_end = min(P, p_begin + pix_per_slab);
-  extern __shared__ float sh[];
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.f;
-  __syncthreads();
-  const size_t n4 = static_cast<size_t>(max(p_end - p_begin, 0)) * Q;
-  // channel quad of a thread is fixed when Q divides the block size: accumulate in registers
-  const bool fixed = (kEwThreads % Q) == 0;
-  float4 a1 = make_float4(0, 0, 0, 0), a2 = make_float4(0, 0, 0, 0);
-  for (size_t i = threadIdx.x; i < n4; i += blockDim.x) {
-    const int q = static_cast<int>(i % Q);
-    const size_t off = (static_cast<size_t>(p_begin) + i / Q) * C + q * 4;
-    const float4 g = ld4(dz + off), v = ld4(y + off);
-    const float4 c01 = ld4(coef + q * 8), c23 = ld4(coef + q * 8 + 4);
-    const float4 s01 = ld4(saved + q * 8), s23 = ld4(saved + q * 8 + 4);
-    float4 s1, s2;
-#define TGB_BN_ACC(f, ca, cb, mu, rs)                                   \
-  {                                                                     \
-    const float dn = (!relu || fmaf(v.f, ca, cb) > 0.f) ? g.f : 0.f;    \
-    s1.f = dn;                                                          \
-    s2.f = dn * ((v.f - (mu)) * (rs));                                  \
-  }
-    TGB_BN_ACC(x, c01.x, c01.y, s01.x, s01.y)
-    TGB_BN_ACC(y, c01.z, c01.w, s01.z, s01.w)
-    TGB_BN_ACC(z, c23.x, c23.y, s23.x, s23.y)
-    TGB_BN_ACC(w, c23.z, c23.w, s23.z, s23.w)
-#undef TGB_BN_ACC
-    if (fixed) {
-      a1.x += s1.x; a1.y += s1.y; a1.z += s1.z; a1.w += s1.w;
-      a2.x += s2.x; a2.y += s2.y; a2.z += s2.z; a2.w += s2.w;
-    } else {
-      float* d = sh + q * 8;
-      atomicAdd(d + 0, s1.x); atomicAdd(d + 1, s2.x); atomicAdd(d + 2, s1.y); atomicAdd(d + 3, s2.y);
-      atomicAdd(d + 4, s1.z); atomicAdd(d + 5, s2.z); atomicAdd(d + 6, s1.w); atomicAdd(d + 7, s2.w);
-    }
-  }
-  if (fixed) {
-    float* d = sh + (threadIdx.x % Q) * 8;
-    atomicAdd(d + 0, a1.x); atomicAdd(d + 1, a2.x); atomicAdd(d + 2, a1.y); atomicAdd(d + 3, a2.y);
-    atomicAdd(d + 4, a1.z); atomicAdd(d + 5, a2.z); atomicAdd(d + 6, a1.w); atomicAdd(d + 7, a2.w);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(sums + i, sh[i]);
-}
+// (the backward reduction lives in bn_reduce.cuh, shared with the residual variant)
 
 // dy = a * (dn - S1/P - xhat * S2/P)
 __global__ void __launch_bounds__(kEwThreads)
@@ -411,11 +362,9 @@ extern "C" int tgb_bn_act_bwd(const float* dz, const float* y, const float* coef
                               const float* saved, float* sums, float* dy, int P, int C, int relu,
                               cudaStream_t stream) {
   if (C % 4) return set_error("bn_act_bwd: C %% 4 != 0");
-  int slabs = sm_count() * 2;
-  if (slabs > (P + 63) / 64) slabs = (P + 63) / 64;
-  if (slabs < 1) slabs = 1;
-  bn_bwd_reduce_kernel<<<slabs, kEwThreads, 2 * C * sizeof(float), stream>>>(
-      dz, y, coef, saved, sums, P, C, slabs, relu);
+  const int slabs = bn_reduce_slabs(P, sm_count());
+  bn_bwd_reduce_generic_kernel<false><<<slabs, kBnReduceThreads, 2 * C * sizeof(float), stream>>>(
+      dz, y, nullptr, coef, saved, sums, P, C, slabs, relu);
   TGB_CHECK_LAUNCH("bn_bwd_reduce");
   const size_t n4 = static_cast<size_t>(P) * (C / 4);
   bn_bwd_apply_kernel<<<ew_grid(n4), kEwThreads, 0, stream>>>(

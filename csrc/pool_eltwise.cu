@@ -18,6 +18,7 @@
 #include <cuda_runtime.h>
 #include <cfloat>
 #include <cstdint>
+#include "bn_reduce.cuh"
 #include "tgb_internal.h"
 
 namespace tgb {
@@ -216,57 +217,6 @@ bn_add_act_fwd_kernel(const float* __restrict__ y, const float* __restrict__ coe
   }
 }
 
-// sums[c] += (sum dn, sum dn * xhat) over a slab of pixels; dn = dz masked by z > 0.
-// Threads own a fixed channel quad when Q divides the block size (register accumulation), and
-// fall back to shared-memory atomics otherwise.
-__global__ void __launch_bounds__(kPeThreads)
-bn_add_act_bwd_reduce_kernel(const float* __restrict__ dz, const float* __restrict__ y,
-                             const float* __restrict__ z, const float* __restrict__ saved,
-                             float* __restrict__ sums, int P, int C, int slabs, int relu) {
-  const int Q = C >> 2;
-  const int per = (P + slabs - 1) / slabs;
-  const int p0 = blockIdx.x * per, p1 = min(P, p0 + per);
-  extern __shared__ float sh[];
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.f;
-  __syncthreads();
-  const size_t n4 = static_cast<size_t>(max(p1 - p0, 0)) * Q;
-  const bool fixed = (kPeThreads % Q) == 0;
-  float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
-  for (size_t i = threadIdx.x; i < n4; i += blockDim.x) {
-    const int q = static_cast<int>(i % Q);
-    const size_t off = (static_cast<size_t>(p0) + i / Q) * C + q * 4;
-    const float4 g4 = pe_ld(dz + off), v4 = pe_ld(y + off), z4 = pe_ld(z + off);
-    const float4 m01 = pe_ld(saved + q * 8), m23 = pe_ld(saved + q * 8 + 4);
-    const float g[4] = {g4.x, g4.y, g4.z, g4.w}, v[4] = {v4.x, v4.y, v4.z, v4.w};
-    const float zz[4] = {z4.x, z4.y, z4.z, z4.w};
-    const float mu[4] = {m01.x, m01.z, m23.x, m23.z}, rs[4] = {m01.y, m01.w, m23.y, m23.w};
-    float a1[4], a2[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float dn = (!relu || zz[k] > 0.f) ? g[k] : 0.f;
-      a1[k] = dn;
-      a2[k] = dn * ((v[k] - mu[k]) * rs[k]);
-    }
-    if (fixed) {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) { s1[k] += a1[k]; s2[k] += a2[k]; }
-    } else {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        atomicAdd(sh + q * 8 + 2 * k, a1[k]);
-        atomicAdd(sh + q * 8 + 2 * k + 1, a2[k]);
-      }
-    }
-  }
-  if (fixed) {
-    float* d = sh + (threadIdx.x % Q) * 8;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { atomicAdd(d + 2 * k, s1[k]); atomicAdd(d + 2 * k + 1, s2[k]); }
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(sums + i, sh[i]);
-}
-
 // dy = a * (dn - S1/P - xhat * S2/P),  dres = dn
 __global__ void __launch_bounds__(kPeThreads)
 bn_add_act_bwd_apply_kernel(const float* __restrict__ dz, const float* __restrict__ y,
@@ -395,11 +345,9 @@ extern "C" int tgb_bn_add_act_bwd(const float* dz, const float* y, const float* 
                                   float* dres, int P, int C, int relu, cudaStream_t stream) {
   if (C % 4) return set_error("bn_add_act_bwd: C %% 4 != 0");
   if (2 * C * sizeof(float) > 48 * 1024) return set_error("bn_add_act_bwd: C too large");
-  int slabs = sm_count() * 2;
-  if (slabs > (P + 63) / 64) slabs = (P + 63) / 64;
-  if (slabs < 1) slabs = 1;
-  bn_add_act_bwd_reduce_kernel<<<slabs, kPeThreads, 2 * C * sizeof(float), stream>>>(
-      dz, y, z, saved, sums, P, C, slabs, relu);
+  const int slabs = bn_reduce_slabs(P, sm_count());
+  bn_bwd_reduce_generic_kernel<true><<<slabs, kBnReduceThreads, 2 * C * sizeof(float), stream>>>(
+      dz, y, z, coef, saved, sums, P, C, slabs, relu);
   TGB_PE_CHECK("bn_add_act_bwd_reduce");
   const size_t n4 = static_cast<size_t>(P) * (C / 4);
   bn_add_act_bwd_apply_kernel<<<pe_grid(n4), kPeThreads, 0, stream>>>(

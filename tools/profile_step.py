@@ -20,24 +20,39 @@ from torch.profiler import ProfilerActivity, profile
 def main():
     p = argparse.ArgumentParser()
     p.add_argument('--no-kernels', action='store_true')
-    p.add_argument('--batch', type=int, default=80)
+    p.add_argument('--model', choices=['unet', 'resnet101', 'amoebanetd'], default='unet')
+    p.add_argument('--batch', type=int, default=None)
     p.add_argument('--chunks', type=int, default=2)
     p.add_argument('--rows', type=int, default=45)
     args = p.parse_args()
 
     from torchgpipe_b200 import GPipe, ops
-    from torchgpipe_b200.models import unet
+    from torchgpipe_b200 import models
     torch.manual_seed(0)
-    model = unet(depth=5, num_convs=5, base_channels=64)
+    if args.model == 'unet':
+        model = models.unet(depth=5, num_convs=5, base_channels=64)
+        batch, hw = args.batch or 80, 192
+    elif args.model == 'resnet101':
+        model = models.resnet101(num_classes=1000)
+        batch, hw = args.batch or 220, 224
+    else:
+        model = models.amoebanetd(num_classes=1000, num_layers=18, num_filters=256)
+        batch, hw = args.batch or 40, 224
     if not args.no_kernels:
         model = ops.convert_to_sm100(model)
-    pipe = GPipe(model, [241], devices=['cuda:0'], chunks=args.chunks, checkpoint='except_last')
+    pipe = GPipe(model, [len(model)], devices=['cuda:0'], chunks=args.chunks,
+                 checkpoint='except_last')
     opt = SGD(pipe.parameters(), lr=0.1)
-    x = torch.rand(args.batch, 3, 192, 192, device='cuda')
-    t = torch.ones(args.batch, 1, 192, 192, device='cuda')
+    x = torch.rand(batch, 3, hw, hw, device='cuda')
+    if args.model == 'unet':
+        t = torch.ones(batch, 1, hw, hw, device='cuda')
+        loss_fn = F.binary_cross_entropy_with_logits
+    else:
+        t = torch.randint(1000, (batch,), device='cuda')
+        loss_fn = F.cross_entropy
 
     def step():
-        loss = F.binary_cross_entropy_with_logits(pipe(x), t)
+        loss = loss_fn(pipe(x), t)
         loss.backward()
         opt.step()
         opt.zero_grad()
