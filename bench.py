@@ -227,7 +227,10 @@ def run_ours(args):
     loss_host = torch.zeros(1).pin_memory()
 
     first, last = rank == 0, rank == world - 1
-    if world == 1:
+    # One rank per stage, every stage pass replayed from CUDA graphs - also for a single stage
+    # (N=1), where the eager single-process GPipe is host-bound (about 2300 launches per step).
+    stage_mode = world > 1 or (n == 1 and not args.no_graphs)
+    if not stage_mode:
         pipe = GPipe(model, balance, devices=[device] * 1 if n == 1 else
                      [torch.device('cuda', k) for k in range(n)],
                      chunks=chunks, checkpoint='except_last')
@@ -244,9 +247,13 @@ def run_ours(args):
             opt.zero_grad()
             return loss
     else:
-        from torchgpipe_b200.distributed import DistributedGPipe, ProcessGroupTransport
+        from torchgpipe_b200.distributed import DistributedGPipe, ProcessGroupTransport, context
         workers = {r: f'stage{r}' for r in range(world)}
-        tp = ProcessGroupTransport(device)
+        if world > 1:
+            tp = ProcessGroupTransport(device)
+        else:
+            tp = None                                   # in-process channels; nothing is sent
+            context.worker(workers[0], chunks).__enter__()
         pipe = DistributedGPipe(model, rank, workers, balance, chunks, device=device,
                                 checkpoint='except_last', transport=tp,
                                 cuda_graphs=not args.no_graphs)
@@ -338,9 +345,11 @@ def run_ours(args):
                    'optimizer': 'SGD(lr=0.1)', 'loss': MODEL_INFO[args.model]['loss'],
                    'parallelism': 'pp%d' % n,
                    'transport': 'single-process' if world == 1 else 'nccl-p2p',
+                   'engine': 'DistributedGPipe (one rank per stage)' if stage_mode
+                   else 'GPipe (single process)',
                    'l2': 'flushed between steps (256 MiB write)',
                    'kernels': 'off' if args.no_kernels else 'sm100',
-                   'cuda_graphs': bool(world > 1 and not args.no_graphs)},
+                   'cuda_graphs': bool(stage_mode and not args.no_graphs)},
         'clocks': clocks,
         'e2e': {'value': e2e_value, 'unit': 'samples/s',
                 'h2d_bytes_per_step': host_input.numel() * 4, 'd2h_bytes_per_step': 4,

@@ -246,6 +246,8 @@ def test_cuda_graph_stage_matches_eager_stage():
     eager, _ = _single_rank_grads(False)
     graphed, pipe = _single_rank_grads(True)
     assert pipe.native_launches_replayed() > 0
+    # 3 steps x 3 micro-batches: the last micro-batch of every step skips its recomputation
+    assert sum(st.recomputes_skipped for st in pipe._graphed.values()) == 3
     for step, ((le, ge), (lg, gg)) in enumerate(zip(eager, graphed)):
         assert rel_err(lg, le) < 5e-3           # same loss trajectory over optimiser steps
         if step == 0:                           # later steps: TF32 noise makes weights diverge
@@ -260,15 +262,24 @@ def test_cuda_graph_recompute_reproduces_dropout_mask():
     cell = ConvInstNormLeaky(nn.Conv2d(32, 64, 3, padding=1, bias=False), 0.5, 1e-5, 0.01).cuda()
     staged = GraphedStage(lambda t: (cell(t[0]),), cell, torch.device('cuda'))
     x = torch.randn(4, 32, 16, 16, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    x2 = torch.randn_like(x).requires_grad_()
     masks = []
-    for _ in range(2):
+    for step in range(2):
         (out,), rng = staged.forward((x,))
+        (out2,), rng2 = staged.forward((x2,))
+        # the latest forward is still resident: its backward needs no recomputation ...
+        gin2, = staged.backward((x2,), rng2, (torch.ones_like(out2),))
+        assert staged.recomputes_skipped == step + 1
+        kept = next(iter(staged._captured.values())).static_outputs[0]
+        assert torch.equal(kept, out2)
+        # ... the earlier one is recomputed and must draw the same dropout mask again
         gin, = staged.backward((x,), rng, (torch.ones_like(out),))
+        assert staged.recomputes_skipped == step + 1
         recomputed = next(iter(staged._captured.values())).static_outputs[0]
         # dropped channels are exactly zero after the norm: same channels in both passes
         assert torch.equal(out == 0, recomputed == 0)
         assert rel_err(recomputed, out) < 1e-3
-        assert torch.isfinite(gin).all()
+        assert torch.isfinite(gin).all() and torch.isfinite(gin2).all()
         masks.append((out == 0).all(dim=3).all(dim=2))
     assert masks[0].any() and not torch.equal(masks[0], masks[1])   # a fresh mask every step
 

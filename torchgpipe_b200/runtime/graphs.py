@@ -16,10 +16,15 @@ per input signature and afterwards issues a whole stage pass with one
   recomputation), replays the backward graph, adds the parameter gradients into
   ``param.grad`` with one fused multi-tensor add and returns the input gradients.
 
-So a graphed stage always checkpoints every micro-batch: it keeps only the stage
-inputs between forward and backward, exactly the memory behaviour of
-``checkpoint='always'`` (reference ``torchgpipe/checkpoint.py``), and one set of
-static activations per stage instead of one per micro-batch.
+So a graphed stage checkpoints every micro-batch: it keeps only the stage inputs
+between forward and backward, the memory behaviour of ``checkpoint='always'``
+(reference ``torchgpipe/checkpoint.py``), and one set of static activations per
+stage instead of one per micro-batch. The exception costs nothing: in the
+fill/drain schedule a stage's last forward (micro-batch m-1) is directly followed
+by the backward of that same micro-batch, whose activations are then still
+resident in the static buffers - ``backward`` notices that and skips the
+recomputation replay, which is ``checkpoint='except_last'`` without holding any
+extra memory.
 
 Everything the native kernels do on the host (tensor-map encoding, launch
 configuration) happens at capture time; derived weights (the tap-flipped dgrad
@@ -83,6 +88,10 @@ class GraphedStage:
         self._shadow = [torch.empty_like(b) for b in self._buffers]
         self.replays = 0
         self.native_launches_replayed = 0
+        # (capture, rng_state object) of the forward replay whose activations are still in the
+        # static buffers; any other replay of this stage (all captures share one pool) clears it
+        self._resident: Optional[Tuple[_Captured, Tensor]] = None
+        self.recomputes_skipped = 0
 
     # -- capture ---------------------------------------------------------------
     def _capture(self, inputs: Sequence[Tensor]) -> _Captured:
@@ -173,6 +182,7 @@ class GraphedStage:
         cap.fwd.replay()
         self.replays += 1
         self.native_launches_replayed += cap.native_launches_fwd
+        self._resident = (cap, rng_state)
         return tuple(o.detach().clone() for o in cap.static_outputs), rng_state
 
     def refresh_derived_weights(self) -> None:
@@ -190,14 +200,24 @@ class GraphedStage:
         cap = self._get(inputs)
         if cap.bwd is None:
             return [None for _ in inputs]
-        if rng_state is not None:
-            torch.cuda.set_rng_state(rng_state, self.device)
-        self._load(cap.static_inputs, inputs)
-        if self._buffers:
-            torch._foreach_copy_(self._shadow, self._buffers)
-        cap.fwd.replay()                         # checkpoint recomputation
-        if self._buffers:
-            torch._foreach_copy_(self._buffers, self._shadow)
+        resident = self._resident
+        self._resident = None
+        if resident is not None and resident[0] is cap and resident[1] is rng_state \
+                and rng_state is not None:
+            # the forward replay of exactly this micro-batch was the last thing this stage ran:
+            # its activations (and static inputs) are still in place
+            self.recomputes_skipped += 1
+            self.replays -= 1
+            self.native_launches_replayed -= cap.native_launches_fwd
+        else:
+            if rng_state is not None:
+                torch.cuda.set_rng_state(rng_state, self.device)
+            self._load(cap.static_inputs, inputs)
+            if self._buffers:
+                torch._foreach_copy_(self._shadow, self._buffers)
+            cap.fwd.replay()                         # checkpoint recomputation
+            if self._buffers:
+                torch._foreach_copy_(self._buffers, self._shadow)
         for s, g in zip(cap.static_grad_outputs, grad_outputs):
             if s is not None:
                 if g is None:
