@@ -151,6 +151,33 @@ upcat_bwd_kernel(const float* __restrict__ dout, float* __restrict__ dx,
   }
 }
 
+// Weights for the data-gradient pass: wt[c][R-1-r][S-1-s][k] = w[k][r][s][c] (both KRSC-style
+// channels-last memory). One 32x32 (k x c) tile of one filter tap per block, transposed through
+// shared memory so that reads (along c) and writes (along k) are both coalesced. Replaces
+// flip + permute + contiguous + copy (three passes, one of them a strided transpose) by one pass.
+__global__ void __launch_bounds__(256)
+dgrad_weight_kernel(const float* __restrict__ w, float* __restrict__ wt, int K, int C, int R,
+                    int S) {
+  __shared__ float tile[32][33];
+  const int tap = blockIdx.z, r = tap / S, s = tap % S;
+  const int tap_out = (R - 1 - r) * S + (S - 1 - s);
+  const int c0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;      // 32 x 8
+  const int RS = R * S;
+#pragma unroll
+  for (int j = 0; j < 32; j += 8) {
+    const int k = k0 + ty + j, c = c0 + tx;
+    tile[ty + j][tx] = (k < K && c < C)
+                           ? w[(static_cast<size_t>(k) * RS + tap) * C + c] : 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 32; j += 8) {
+    const int c = c0 + ty + j, k = k0 + tx;
+    if (c < C && k < K) wt[(static_cast<size_t>(c) * RS + tap_out) * K + k] = tile[tx][ty + j];
+  }
+}
+
 static int pr_grid(size_t n) {
   size_t blocks = (n + kPrThreads - 1) / kPrThreads;
   const size_t cap = static_cast<size_t>(sm_count()) * 16;
@@ -212,5 +239,16 @@ extern "C" int tgb_upsample2x_cat_bwd(const float* dout, float* dx, float* dskip
   upcat_bwd_kernel<<<pr_grid(n), kPrThreads, 0, stream>>>(dout, dx, dskip, N, Hx, Wx, C1, Hs, Ws,
                                                           C2);
   TGB_PR_CHECK("upsample2x_cat_bwd");
+  return 0;
+}
+
+extern "C" int tgb_dgrad_weight(const float* w, float* wt, int K, int C, int R, int S,
+                                cudaStream_t stream) {
+  if (K < 1 || C < 1 || R < 1 || S < 1 || R * S > 65535)
+    return set_error("dgrad_weight: bad filter shape");
+  const dim3 grid((C + 31) / 32, (K + 31) / 32, R * S);
+  if (grid.y > 65535) return set_error("dgrad_weight: K too large");
+  dgrad_weight_kernel<<<grid, 256, 0, stream>>>(w, wt, K, C, R, S);
+  TGB_PR_CHECK("dgrad_weight");
   return 0;
 }

@@ -133,6 +133,11 @@ int tgb_upsample2x_cat_fwd(const float* x, const float* skip, float* out, int N,
 int tgb_upsample2x_cat_bwd(const float* dout, float* dx, float* dskip, int N, int Hx, int Wx,
                            int C1, int Hs, int Ws, int C2, cudaStream_t stream);
 
+/* Weights of the data-gradient pass: wt[c][R-1-r][S-1-s][k] = w[k][r][s][c] (tap flip + channel
+ * transpose, KRSC memory on both sides) in one coalesced pass; the dgrad of a stride-1
+ * convolution is then tgb_conv2d_fprop_tf32(dy, wt). */
+int tgb_dgrad_weight(const float* w, float* wt, int K, int C, int R, int S, cudaStream_t stream);
+
 /* NHWC fp32 pooling family and residual joins (C multiple of 4; n multiple of 4).
  * tgb_pool2d_fwd/bwd: k x k window, stride s, zero padding p (2p <= k), floor output size.
  *   mode 0 max, 1 average over the valid (non-padding) pixels (count_include_pad=False),

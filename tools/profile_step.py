@@ -24,6 +24,8 @@ def main():
     p.add_argument('--batch', type=int, default=None)
     p.add_argument('--chunks', type=int, default=2)
     p.add_argument('--rows', type=int, default=45)
+    p.add_argument('--graphs', action='store_true',
+                   help='the graph-replayed stage engine (what bench.py runs) instead of eager GPipe')
     args = p.parse_args()
 
     from torchgpipe_b200 import GPipe, ops
@@ -40,9 +42,6 @@ def main():
         batch, hw = args.batch or 40, 224
     if not args.no_kernels:
         model = ops.convert_to_sm100(model)
-    pipe = GPipe(model, [len(model)], devices=['cuda:0'], chunks=args.chunks,
-                 checkpoint='except_last')
-    opt = SGD(pipe.parameters(), lr=0.1)
     x = torch.rand(batch, 3, hw, hw, device='cuda')
     if args.model == 'unet':
         t = torch.ones(batch, 1, hw, hw, device='cuda')
@@ -51,11 +50,30 @@ def main():
         t = torch.randint(1000, (batch,), device='cuda')
         loss_fn = F.cross_entropy
 
-    def step():
-        loss = loss_fn(pipe(x), t)
-        loss.backward()
-        opt.step()
-        opt.zero_grad()
+    if args.graphs:
+        from torchgpipe_b200.distributed import DistributedGPipe, context
+        context.worker('solo', args.chunks).__enter__()
+        pipe = DistributedGPipe(model, 0, {0: 'solo'}, [len(model)], args.chunks,
+                                device=torch.device('cuda:0'), checkpoint='except_last',
+                                cuda_graphs=True)
+        opt = SGD(pipe.model().parameters(), lr=0.1)
+        scale = 1.0 / args.chunks
+
+        def step():
+            outs = pipe.forward(x)
+            pipe.backward([loss_fn(o, tt) * scale for o, tt in zip(outs, t.chunk(args.chunks))])
+            opt.step()
+            opt.zero_grad()
+    else:
+        pipe = GPipe(model, [len(model)], devices=['cuda:0'], chunks=args.chunks,
+                     checkpoint='except_last')
+        opt = SGD(pipe.parameters(), lr=0.1)
+
+        def step():
+            loss = loss_fn(pipe(x), t)
+            loss.backward()
+            opt.step()
+            opt.zero_grad()
 
     for _ in range(2):
         step()

@@ -91,12 +91,18 @@ def _dgrad_weight(w: Tensor, cache: Optional[dict]) -> Tensor:
     if cache is not None:
         if cache.get('version') == w._version and cache.get('ptr') == w.data_ptr():
             return cache['wt']
-    wt = _cl(w.detach().flip(2, 3).permute(1, 0, 2, 3))
+    K, C, R, S = w.shape
+    old = cache.get('wt') if cache is not None else None
+    if old is not None and old.shape == (C, K, R, S) and old.device == w.device:
+        wt = old                # keep the address: captured CUDA graphs read this buffer
+    else:
+        wt = torch.empty((C, K, R, S), device=w.device, dtype=torch.float32, memory_format=_CL)
+    src = _cl(w.detach())
+    with torch.cuda.device(w.device):
+        rc = _lib.require().tgb_dgrad_weight(_lib.ptr(src), _lib.ptr(wt), _c_int(K), _c_int(C),
+                                             _c_int(R), _c_int(S), _lib.stream_ptr(w.device))
+    _lib.check(rc, 'tgb_dgrad_weight')
     if cache is not None:
-        old = cache.get('wt')
-        if old is not None and old.shape == wt.shape and old.device == wt.device:
-            old.copy_(wt)       # keep the address: captured CUDA graphs read this buffer
-            wt = old
         cache['version'], cache['ptr'], cache['wt'] = w._version, w.data_ptr(), wt
     return wt
 
