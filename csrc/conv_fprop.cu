@@ -349,21 +349,27 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
 }
 
 // ---------------------------------------------------------------- host side
-static void choose_pixel_box(int N, int Ho, int Wo, int& BW, int& BH, int& BNB) {
+static void choose_pixel_box(int N, int Ho, int Wo, int stats_mode, int& BW, int& BH, int& BNB) {
   // Largest-utilisation box with BW*BH*BNB <= 128 that wastes the fewest rows on partial tiles.
   double best = -1.0;
   BW = 1; BH = 1; BNB = 1;
   for (int bw = 1; bw <= Wo && bw <= 128; ++bw) {
     for (int bh = 1; bh <= Ho && bw * bh <= 128; ++bh) {
-      int max_nb = 128 / (bw * bh);
-      // only batch several images into a tile when the tile already covers a whole image
-      int nb_hi = (bw == Wo && bh == Ho) ? max_nb : 1;
+      // Several images per tile: whole small images (6x6 -> 3 images), or the same row band of
+      // several images when one image does not divide into 128-pixel boxes (12x12 = 144 pixels:
+      // a 12x10 box leaves 44 % of the MMA rows empty, 12x2 x 5 images fills 120 of 128).
+      // Bands keep full-width rows so every TMA row is one contiguous run.
+      const int max_nb = 128 / (bw * bh);
+      const int nb_hi = (bw == Wo) ? max_nb : 1;
       for (int nb = 1; nb <= nb_hi && nb <= N; ++nb) {
         const long tiles = static_cast<long>((Wo + bw - 1) / bw) * ((Ho + bh - 1) / bh) *
                            ((N + nb - 1) / nb);
         const double useful = static_cast<double>(N) * Ho * Wo / (static_cast<double>(tiles) * 128);
-        // prefer wide boxes (longer contiguous runs per TMA row) on ties
-        const double score = useful + 1e-6 * bw;
+        // on ties prefer wide boxes (longer contiguous runs per TMA row), then few images per
+        // tile (fewer statistics segments in the epilogue)
+        // Per-image statistics (mode 1) cost one pair of global atomics per column and image
+        // segment in the epilogue: there an extra image per tile must buy 2.5 % utilisation.
+        const double score = useful + 1e-6 * bw - (stats_mode == 1 ? 0.025 : 1e-8) * (nb - 1);
         if (score > best) {
           best = score;
           BW = bw; BH = bh; BNB = nb;
@@ -420,7 +426,7 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
   g.Ho = H + 2 * pad_h - R + 1;
   g.Wo = W + 2 * pad_w - S + 1;
   if (g.Ho <= 0 || g.Wo <= 0) return set_error("conv_fprop: empty output");
-  choose_pixel_box(N, g.Ho, g.Wo, g.BW, g.BH, g.BNB);
+  choose_pixel_box(N, g.Ho, g.Wo, stats ? stats_mode : 0, g.BW, g.BH, g.BNB);
   // Output-channel tile: the widest of {256,128,64,32} that wastes at most 1/8 of its columns.
   // A partial last tile is fine: weight rows past K are zero-filled by TMA and the store of
   // columns past K is clipped.
@@ -442,11 +448,31 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
   const int base_tiles = g.tiles_w * g.tiles_h * g.tiles_n * g.tiles_k;
   const int k_iters = R * S * g.c_blocks;
   g.splits = 1;
-  if (base_tiles * 2 <= sms && k_iters >= 32 && getenv("TGB_FPROP_NOSPLIT") == nullptr) {
-    int splits = sms / base_tiles;
-    if (splits > k_iters / 16) splits = k_iters / 16;
-    if (splits > 8) splits = 8;
-    if (splits > 1) g.splits = splits;
+  if (k_iters >= 32 && getenv("TGB_FPROP_NOSPLIT") == nullptr) {
+    // Wave model: `items` equal work items run in ceil(items / sms) waves; an item costs its
+    // reduction iterations plus an epilogue worth about kEpi iterations. Splitting the reduction
+    // s ways shortens the items and fills partial waves (90 tiles on 148 SMs leave 39 % of the
+    // machine idle) at the price of a zero-fill of Y, s reduce-add epilogues per tile and - when
+    // statistics are wanted - one more pass over Y. Take the cheapest s, if it wins by > 5 %.
+    constexpr int kEpi = 8;
+    const double y_pass = static_cast<double>(N) * g.Ho * g.Wo * K * 4.0 / 6.0e12 / 0.4e-6;
+    double best = static_cast<double>((base_tiles + sms - 1) / sms) * (k_iters + kEpi);
+    for (int sp = 2; sp <= 8 && k_iters / sp >= 16; ++sp) {
+      const int iters = (k_iters + sp - 1) / sp;
+      const int eff = (k_iters + iters - 1) / iters;
+      const long long items = static_cast<long long>(base_tiles) * eff;
+      double cost = static_cast<double>((items + sms - 1) / sms) * (iters + kEpi);
+      cost += 4.0 + y_pass;                                   // memset + launch
+      if (g.stats_mode != 0) cost += 12.0 + y_pass;           // separate moments pass
+      if (cost * 1.05 < best) {
+        best = cost;
+        g.splits = eff;
+      }
+    }
+    if (const char* force = getenv("TGB_FPROP_SPLITS")) {
+      const int f = atoi(force);
+      if (f >= 1 && f <= 8) g.splits = f;
+    }
   }
   g.iters_per_split = (k_iters + g.splits - 1) / g.splits;
   g.splits = (k_iters + g.iters_per_split - 1) / g.iters_per_split;

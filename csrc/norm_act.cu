@@ -31,8 +31,7 @@ template <int MODE>
 __global__ void __launch_bounds__(kEwThreads)
 moments_kernel(const float* __restrict__ a, const float* __restrict__ b,
                float* __restrict__ out, int P, int C, int slabs, float slope) {
-  // grid: (slabs, G). Thread t owns channel quad (t % Q) when Q divides the block size,
-  // otherwise quads are re-derived per element.
+  // grid: (slabs, G)
   const int g = blockIdx.y;
   const int Q = C >> 2;
   const size_t base = static_cast<size_t>(g) * P * C;
@@ -44,20 +43,25 @@ moments_kernel(const float* __restrict__ a, const float* __restrict__ b,
   __syncthreads();
 
   const float inv_slope = 1.f / slope;
-  if (kEwThreads % Q == 0) {
-    const int q = threadIdx.x % Q;
-    const int lanes_per_pixel = Q;
-    const int pix_step = kEwThreads / lanes_per_pixel;
-    float4 s1 = make_float4(0, 0, 0, 0), s2 = make_float4(0, 0, 0, 0);
-    for (int p = p_begin + threadIdx.x / lanes_per_pixel; p < p_end; p += pix_step) {
-      const size_t off = base + static_cast<size_t>(p) * C + q * 4;
-      const float4 va = ld4(a + off);
-      if (MODE == 0) {
-        s1.x += va.x; s1.y += va.y; s1.z += va.z; s1.w += va.w;
-        s2.x = fmaf(va.x, va.x, s2.x); s2.y = fmaf(va.y, va.y, s2.y);
-        s2.z = fmaf(va.z, va.z, s2.z); s2.w = fmaf(va.w, va.w, s2.w);
-      } else if (MODE == 1) {
-        const float4 vz = ld4(b + off);
+  // No per-element integer division: a thread's channel quad is fixed. Q <= 256: quad = tid % Q
+  // and floor(256/Q) pixel lanes walk the slab together; Q > 256: the thread owns quads
+  // tid, tid+256, ... and walks the slab's pixels alone. Rows are read as coalesced float4.
+  const int lanes = Q <= kEwThreads ? kEwThreads / Q : 1;
+  const int lane = Q <= kEwThreads ? threadIdx.x / Q : 0;
+  const int q_step = Q <= kEwThreads ? Q : kEwThreads;      // one pass when Q <= 256
+  if (lane < lanes) {
+    for (int q = Q <= kEwThreads ? threadIdx.x % Q : threadIdx.x; q < Q; q += q_step) {
+      float4 s1 = make_float4(0, 0, 0, 0), s2 = make_float4(0, 0, 0, 0);
+#pragma unroll 4
+      for (int p = p_begin + lane; p < p_end; p += lanes) {
+        const size_t off = base + static_cast<size_t>(p) * C + q * 4;
+        const float4 va = ld4(a + off);
+        if (MODE == 0) {
+          s1.x += va.x; s1.y += va.y; s1.z += va.z; s1.w += va.w;
+          s2.x = fmaf(va.x, va.x, s2.x); s2.y = fmaf(va.y, va.y, s2.y);
+          s2.z = fmaf(va.z, va.z, s2.z); s2.w = fmaf(va.w, va.w, s2.w);
+        } else if (MODE == 1) {
+          const float4 vz = ld4(b + off);
 #define TGB_ACC1(f)                                              \
   {                                                              \
     const float dn = vz.f > 0.f ? va.f : va.f * slope;           \
@@ -65,42 +69,16 @@ moments_kernel(const float* __restrict__ a, const float* __restrict__ b,
     s1.f += dn;                                                  \
     s2.f = fmaf(dn, u, s2.f);                                    \
   }
-        TGB_ACC1(x) TGB_ACC1(y) TGB_ACC1(z) TGB_ACC1(w)
+          TGB_ACC1(x) TGB_ACC1(y) TGB_ACC1(z) TGB_ACC1(w)
 #undef TGB_ACC1
-      }
-    }
-    float* d = sh + q * 8;
-    atomicAdd(d + 0, s1.x); atomicAdd(d + 1, s2.x);
-    atomicAdd(d + 2, s1.y); atomicAdd(d + 3, s2.y);
-    atomicAdd(d + 4, s1.z); atomicAdd(d + 5, s2.z);
-    atomicAdd(d + 6, s1.w); atomicAdd(d + 7, s2.w);
-  } else {
-    const size_t n4 = static_cast<size_t>(p_end - p_begin) * Q;
-    for (size_t i = threadIdx.x; i < n4; i += blockDim.x) {
-      const int q = static_cast<int>(i % Q);
-      const size_t off = base + (static_cast<size_t>(p_begin) + i / Q) * C + q * 4;
-      const float4 va = ld4(a + off);
-      float4 s1, s2;
-      if (MODE == 0) {
-        s1 = va;
-        s2 = make_float4(va.x * va.x, va.y * va.y, va.z * va.z, va.w * va.w);
-      } else {
-        const float4 vz = ld4(b + off);
-#define TGB_ONE(f)                                               \
-  {                                                              \
-    const float dn = vz.f > 0.f ? va.f : va.f * slope;           \
-    const float u = vz.f > 0.f ? vz.f : vz.f * inv_slope;        \
-    s1.f = dn;                                                   \
-    s2.f = dn * u;                                               \
-  }
-        TGB_ONE(x) TGB_ONE(y) TGB_ONE(z) TGB_ONE(w)
-#undef TGB_ONE
+        }
       }
       float* d = sh + q * 8;
       atomicAdd(d + 0, s1.x); atomicAdd(d + 1, s2.x);
       atomicAdd(d + 2, s1.y); atomicAdd(d + 3, s2.y);
       atomicAdd(d + 4, s1.z); atomicAdd(d + 5, s2.z);
       atomicAdd(d + 6, s1.w); atomicAdd(d + 7, s2.w);
+      if (Q <= kEwThreads) break;
     }
   }
   __syncthreads();
