@@ -49,11 +49,22 @@ struct ConvGeom {
   int splits, iters_per_split;      // split of the reduction (taps x channel blocks) over CTAs
 };
 
-template <int BN, int STAGES>
+// HALO variant (filters up to 3x3, BN <= 64): the tile is 8 pixels wide x 16 rows and a stage
+// holds, for one 32-channel block, the input tile WITH its halo ((8+S-1) x (16+R-1) pixels, one
+// TMA box) plus the weights of all R*S taps. The A operand of tap (r,s) is the same shared-memory
+// tile read through a descriptor that starts (r*pitch + s) rows in and steps pitch rows per
+// 8-row group (SBO = pitch * 128 B): 8 consecutive pixels of an image row are 8 consecutive smem
+// rows, the next image row starts one pitch later. tcgen05 applies the 128B swizzle to absolute
+// shared-memory addresses, so a descriptor may start at any 128-byte row of a TMA-written tile.
+// The input is then read once per tile instead of once per tap (6.25x less A traffic for 3x3).
+constexpr int kHaloW = 8, kHaloH = 16, kHaloMaxTaps = 9;
+constexpr int kHaloABytes = ((kHaloW + 2) * (kHaloH + 2) * kBlockKBytes + 1023) / 1024 * 1024;
+
+template <int BN, int STAGES, bool HALO = false>
 struct SmemLayout {
-  static constexpr int kABytes = kBlockM * kBlockKBytes;       // 16 KB
-  static constexpr int kBBytes = BN * kBlockKBytes;
-  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kABytes = HALO ? kHaloABytes : kBlockM * kBlockKBytes;   // 16 KB / 23 KB
+  static constexpr int kBBytes = BN * kBlockKBytes;                             // one tap
+  static constexpr int kStageBytes = kABytes + (HALO ? kHaloMaxTaps : 1) * kBBytes;
   static constexpr int kEpiBytes = kBlockM * kBlockKBytes;     // 16 KB per staging buffer
   static constexpr int kEpiOffset = STAGES * kStageBytes;
   static constexpr int kStatOffset = kEpiOffset + 2 * kEpiBytes;   // 1 KB partials + 512 B table
@@ -61,13 +72,13 @@ struct SmemLayout {
   static constexpr int kTotal = kBarOffset + (2 * STAGES + 4) * 8 + 16;
 };
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, bool HALO = false>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
                        const __grid_constant__ CUtensorMap tmap_w,
                        const __grid_constant__ CUtensorMap tmap_y,
                        const ConvGeom g, float* __restrict__ stats) {
-  using L = SmemLayout<BN, STAGES>;
+  using L = SmemLayout<BN, STAGES, HALO>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // dynamic smem is only guaranteed 16B aligned: round up to the 1024B the swizzle needs
   uint8_t* smem = reinterpret_cast<uint8_t*>(
@@ -83,8 +94,14 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
   const int lane = threadIdx.x & 31;
   const int rows_valid = g.BW * g.BH * g.BNB;
   const int num_tiles = g.tiles_w * g.tiles_h * g.tiles_n * g.tiles_k * g.splits;
-  const int k_iters = g.R * g.S * g.c_blocks;
-  const uint32_t stage_tx = static_cast<uint32_t>(rows_valid * kBlockKBytes + L::kBBytes);
+  const int taps = g.R * g.S;
+  // HALO: one iteration per channel block (all taps inside); otherwise per (tap, channel block)
+  const int k_iters = HALO ? g.c_blocks : taps * g.c_blocks;
+  const int halo_pitch = g.BW + g.S - 1;                        // pixels per haloed tile row
+  const uint32_t stage_tx =
+      HALO ? static_cast<uint32_t>(halo_pitch * (g.BH + g.R - 1) * kBlockKBytes +
+                                   taps * L::kBBytes)
+           : static_cast<uint32_t>(rows_valid * kBlockKBytes + L::kBBytes);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_x);
@@ -138,6 +155,24 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
         const int h0 = th * g.BH - g.pad_h;
         const int n0 = tn * g.BNB;
         const int k0 = kt * BN;
+        if (HALO) {
+          // one haloed input box and the weights of every tap per channel block
+          for (int cb = it_begin; cb < it_end; ++cb) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            uint8_t* a_dst = smem + stage * L::kStageBytes;
+            uint8_t* b_dst = a_dst + L::kABytes;
+            mbar_expect_tx(&full_bar[stage], stage_tx);
+            tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cb * kBlockK, w0, h0, n0);
+            for (int t = 0; t < taps; ++t)
+              tma_load_4d(b_dst + t * L::kBBytes, &tmap_w, &full_bar[stage], cb * kBlockK, t, k0,
+                          0);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+          continue;
+        }
         int tap = it_begin / g.c_blocks;
         int cb = it_begin - tap * g.c_blocks;
         for (int it = it_begin; it < it_end; ++it) {
@@ -181,13 +216,29 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
           const uint32_t b_addr = a_addr + L::kABytes;
-          const uint64_t a_desc = make_smem_desc_sw128(a_addr, 16, 1024);
-          const uint64_t b_desc = make_smem_desc_sw128(b_addr, 16, 1024);
+          if (HALO) {
+            // tap (r,s) reads the haloed tile (r*pitch + s) rows in; 8-row groups (= 8 pixels of
+            // one image row) are one haloed row apart
+            const uint32_t sbo = static_cast<uint32_t>(halo_pitch * kBlockKBytes);
+            for (int t = 0; t < taps; ++t) {
+              const int r = t / g.S, sft = t - r * g.S;
+              const uint64_t a_desc = make_smem_desc_sw128(
+                  a_addr + static_cast<uint32_t>((r * halo_pitch + sft) * kBlockKBytes), 16, sbo);
+              const uint64_t b_desc = make_smem_desc_sw128(b_addr + t * L::kBBytes, 16, 1024);
 #pragma unroll
-          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-            // advance 32 bytes inside the 128B swizzle row: +2 in the (addr >> 4) field
-            mma_tf32_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc,
-                        (it > 0 || k > 0) ? 1u : 0u);
+              for (int k = 0; k < kBlockK / kUmmaK; ++k)
+                mma_tf32_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc,
+                            (it > 0 || t > 0 || k > 0) ? 1u : 0u);
+            }
+          } else {
+            const uint64_t a_desc = make_smem_desc_sw128(a_addr, 16, 1024);
+            const uint64_t b_desc = make_smem_desc_sw128(b_addr, 16, 1024);
+#pragma unroll
+            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+              // advance 32 bytes inside the 128B swizzle row: +2 in the (addr >> 4) field
+              mma_tf32_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc,
+                          (it > 0 || k > 0) ? 1u : 0u);
+            }
           }
           mma_commit(&empty_bar[stage]);                  // smem slot free once MMAs retire
           if (it == n_it - 1) mma_commit(&tmem_full[acc]);
@@ -379,10 +430,10 @@ static void choose_pixel_box(int N, int Ho, int Wo, int stats_mode, int& BW, int
   }
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, bool HALO = false>
 static int launch_fprop(const CUtensorMap& mx, const CUtensorMap& mw, const CUtensorMap& my,
                         const ConvGeom& g, float* stats, int sm_count, cudaStream_t stream) {
-  using L = SmemLayout<BN, STAGES>;
+  using L = SmemLayout<BN, STAGES, HALO>;
   constexpr int smem_bytes = L::kTotal + 1024;      // + alignment slack
   // the opt-in shared-memory size is a per-device attribute of the kernel: one process may
   // drive several GPUs (single-process GPipe), so remember it per device
@@ -391,7 +442,7 @@ static int launch_fprop(const CUtensorMap& mx, const CUtensorMap& mw, const CUte
   cudaGetDevice(&dev_);
   if (dev_ < 0 || dev_ >= 64) dev_ = 0;
   bool& configured = configured_on[dev_];
-  auto kern = conv_fprop_tf32_kernel<BN, STAGES>;
+  auto kern = conv_fprop_tf32_kernel<BN, STAGES, HALO>;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          smem_bytes);
@@ -435,6 +486,24 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
     const int tiles = (K + cand - 1) / cand;
     if ((tiles * cand - K) * 8 <= tiles * cand) { BN = cand; break; }
   }
+  // Narrow output tiles (BN <= 64) are bound by L2 -> SM traffic when every tap re-reads the
+  // input: use the haloed-tile variant (8 x 16 pixel tiles, input read once per tile) when the
+  // filter is at most 3x3, the image tiles well into 8 x 16 boxes and there are plenty of tiles.
+  bool halo = false;
+  if (BN <= 64 && R <= 3 && S <= 3 && R * S > 1) {
+    const long tw8 = (g.Wo + kHaloW - 1) / kHaloW, th16 = (g.Ho + kHaloH - 1) / kHaloH;
+    const double useful = static_cast<double>(g.Ho) * g.Wo / (tw8 * kHaloW * th16 * kHaloH);
+    halo = useful >= 0.85 && tw8 * th16 * N * ((K + BN - 1) / BN) >= 4L * sm_count();
+    if (const char* env = getenv("TGB_FPROP_HALO")) {     // 0: never, 2: whenever it can run
+      const int mode = atoi(env);
+      halo = mode == 2 ? true : (mode != 0 && halo);
+    }
+    if (halo) {
+      g.BW = kHaloW;
+      g.BH = kHaloH;
+      g.BNB = 1;
+    }
+  }
   g.tiles_w = (g.Wo + g.BW - 1) / g.BW;
   g.tiles_h = (g.Ho + g.BH - 1) / g.BH;
   g.tiles_n = (N + g.BNB - 1) / g.BNB;
@@ -446,9 +515,9 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
   // whole GPU works; partial sums are combined by TMA reduce-add into a zeroed Y.
   const int sms = sm_count();
   const int base_tiles = g.tiles_w * g.tiles_h * g.tiles_n * g.tiles_k;
-  const int k_iters = R * S * g.c_blocks;
+  const int k_iters = halo ? g.c_blocks : R * S * g.c_blocks;
   g.splits = 1;
-  if (k_iters >= 32 && getenv("TGB_FPROP_NOSPLIT") == nullptr) {
+  if (!halo && k_iters >= 32 && getenv("TGB_FPROP_NOSPLIT") == nullptr) {
     // Wave model: `items` equal work items run in ceil(items / sms) waves; an item costs its
     // reduction iterations plus an epilogue worth about kEpi iterations. Splitting the reduction
     // s ways shortens the items and fills partial waves (90 tiles on 148 SMs leave 39 % of the
@@ -489,6 +558,10 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
     uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
     uint64_t strides[3] = {(uint64_t)C * 4, (uint64_t)W * C * 4, (uint64_t)H * W * C * 4};
     uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
+    if (halo) {               // the input tile with its halo in one box
+      box[1] = (uint32_t)(g.BW + S - 1);
+      box[2] = (uint32_t)(g.BH + R - 1);
+    }
     if (make_tensor_map(&mx, x, 4, 4, dims, strides, box, 1))
       return set_error("conv_fprop: tensor map for X failed");
   }
@@ -510,6 +583,10 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
       return set_error("conv_fprop: tensor map for Y failed");
   }
   int rc;
+  if (halo) {
+    rc = BN == 64 ? launch_fprop<64, 2, true>(mx, mw, my, g, stats, sms, stream)
+                  : launch_fprop<32, 3, true>(mx, mw, my, g, stats, sms, stream);
+  } else
   switch (BN) {
     case 256: rc = launch_fprop<256, 4>(mx, mw, my, g, stats, sms, stream); break;
     case 128: rc = launch_fprop<128, 6>(mx, mw, my, g, stats, sms, stream); break;

@@ -335,6 +335,21 @@ int main(int argc, char** argv) {
     fails += run_conv_case(c, true, 0);
     fails += run_wgrad_case(c, true, 0);
   }
+  // haloed-tile forward variant (8x16 pixel tiles, input read once per tile), forced on
+  ConvCase halo_cases[] = {
+      {"halo_64_64", 2, 40, 24, 64, 64, 3, 3, 1, 1, 1},
+      {"halo_48_32", 3, 16, 20, 48, 32, 3, 3, 1, 1, 2},
+      {"halo_128_32_pad0", 1, 34, 18, 128, 32, 3, 3, 0, 0, 0},
+      {"halo_1x3", 2, 16, 16, 32, 64, 1, 3, 0, 1, 1},
+      {"halo_3x1_k40", 2, 18, 9, 32, 40, 3, 1, 1, 0, 0},
+      {"halo_dgrad_pad", 2, 20, 12, 64, 64, 3, 3, 2, 2, 0},
+  };
+  for (auto& c : halo_cases) {
+    if (only && strcmp(only, c.name) && strcmp(only, "all") && strcmp(only, "halo")) continue;
+    setenv("TGB_FPROP_HALO", "2", 1);
+    fails += run_conv_case(c, true, 0);
+    unsetenv("TGB_FPROP_HALO");
+  }
   ConvCase perf[] = {
       {"perf_64_192", 8, 192, 192, 64, 64, 3, 3, 1, 1, 0},
       {"perf_128_96", 16, 96, 96, 128, 128, 3, 3, 1, 1, 0},
