@@ -60,25 +60,31 @@ struct ConvGeom {
 constexpr int kHaloW = 8, kHaloH = 16, kHaloMaxTaps = 9;
 constexpr int kHaloABytes = ((kHaloW + 2) * (kHaloH + 2) * kBlockKBytes + 1023) / 1024 * 1024;
 
-template <int BN, int STAGES, bool HALO = false>
+// RESW (with HALO, all output channels in one tile): the whole filter bank (<= 144 KB: 64->64,
+// 128->32, 32->32 at 3x3) is loaded into shared memory once per CTA and stays there for all of
+// its tiles; the stages then carry only the 23 KB haloed input tile.
+constexpr int kResidentWBytes = 147456;
+
+template <int BN, int STAGES, bool HALO = false, bool RESW = false>
 struct SmemLayout {
   static constexpr int kABytes = HALO ? kHaloABytes : kBlockM * kBlockKBytes;   // 16 KB / 23 KB
   static constexpr int kBBytes = BN * kBlockKBytes;                             // one tap
-  static constexpr int kStageBytes = kABytes + (HALO ? kHaloMaxTaps : 1) * kBBytes;
+  static constexpr int kStageBytes = kABytes + (RESW ? 0 : (HALO ? kHaloMaxTaps : 1) * kBBytes);
+  static constexpr int kWOffset = STAGES * kStageBytes;        // resident filter bank (RESW)
   static constexpr int kEpiBytes = kBlockM * kBlockKBytes;     // 16 KB per staging buffer
-  static constexpr int kEpiOffset = STAGES * kStageBytes;
+  static constexpr int kEpiOffset = kWOffset + (RESW ? kResidentWBytes : 0);
   static constexpr int kStatOffset = kEpiOffset + 2 * kEpiBytes;   // 1 KB partials + 512 B table
   static constexpr int kBarOffset = kStatOffset + 1536;
-  static constexpr int kTotal = kBarOffset + (2 * STAGES + 4) * 8 + 16;
+  static constexpr int kTotal = kBarOffset + (2 * STAGES + 5) * 8 + 16;
 };
 
-template <int BN, int STAGES, bool HALO = false>
+template <int BN, int STAGES, bool HALO = false, bool RESW = false>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
                        const __grid_constant__ CUtensorMap tmap_w,
                        const __grid_constant__ CUtensorMap tmap_y,
                        const ConvGeom g, float* __restrict__ stats) {
-  using L = SmemLayout<BN, STAGES, HALO>;
+  using L = SmemLayout<BN, STAGES, HALO, RESW>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // dynamic smem is only guaranteed 16B aligned: round up to the 1024B the swizzle needs
   uint8_t* smem = reinterpret_cast<uint8_t*>(
@@ -88,7 +94,8 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full = empty_bar + STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* w_bar = tmem_empty + 2;                 // resident filter bank has landed (RESW)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_bar + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -100,7 +107,7 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
   const int halo_pitch = g.BW + g.S - 1;                        // pixels per haloed tile row
   const uint32_t stage_tx =
       HALO ? static_cast<uint32_t>(halo_pitch * (g.BH + g.R - 1) * kBlockKBytes +
-                                   taps * L::kBBytes)
+                                   (RESW ? 0 : taps * L::kBBytes))
            : static_cast<uint32_t>(rows_valid * kBlockKBytes + L::kBBytes);
 
   if (warp == 0 && lane == 0) {
@@ -117,6 +124,7 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
       mbar_init(&tmem_full[s], 1);
       mbar_init(&tmem_empty[s], 4);       // one arrival per epilogue warp
     }
+    mbar_init(w_bar, 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -148,6 +156,14 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      if (RESW && static_cast<int>(blockIdx.x) < num_tiles) {
+        // the filter bank, [channel block][tap][BN rows x 128 B], once per CTA
+        mbar_expect_tx(w_bar, static_cast<uint32_t>(g.c_blocks * taps * L::kBBytes));
+        for (int cb = 0; cb < g.c_blocks; ++cb)
+          for (int t = 0; t < taps; ++t)
+            tma_load_4d(smem + L::kWOffset + (cb * taps + t) * L::kBBytes, &tmap_w, w_bar,
+                        cb * kBlockK, t, 0, 0);
+      }
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int kt, tw, th, tn;
         decode_tile(tile, kt, tw, th, tn);
@@ -163,9 +179,10 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
             uint8_t* b_dst = a_dst + L::kABytes;
             mbar_expect_tx(&full_bar[stage], stage_tx);
             tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cb * kBlockK, w0, h0, n0);
-            for (int t = 0; t < taps; ++t)
-              tma_load_4d(b_dst + t * L::kBBytes, &tmap_w, &full_bar[stage], cb * kBlockK, t, k0,
-                          0);
+            if (!RESW)
+              for (int t = 0; t < taps; ++t)
+                tma_load_4d(b_dst + t * L::kBBytes, &tmap_w, &full_bar[stage], cb * kBlockK, t,
+                            k0, 0);
             if (++stage == STAGES) {
               stage = 0;
               phase ^= 1;
@@ -204,6 +221,10 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      if (RESW && static_cast<int>(blockIdx.x) < num_tiles) {
+        mbar_wait(w_bar, 0);
+        tc_fence_after();
+      }
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int kt_, tw_, th_, tn_;
         decode_tile(tile, kt_, tw_, th_, tn_);            // sets [it_begin, it_end)
@@ -224,7 +245,10 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
               const int r = t / g.S, sft = t - r * g.S;
               const uint64_t a_desc = make_smem_desc_sw128(
                   a_addr + static_cast<uint32_t>((r * halo_pitch + sft) * kBlockKBytes), 16, sbo);
-              const uint64_t b_desc = make_smem_desc_sw128(b_addr + t * L::kBBytes, 16, 1024);
+              const uint32_t bt_addr =
+                  RESW ? smem_u32(smem + L::kWOffset) + (it * taps + t) * L::kBBytes
+                       : b_addr + t * L::kBBytes;
+              const uint64_t b_desc = make_smem_desc_sw128(bt_addr, 16, 1024);
 #pragma unroll
               for (int k = 0; k < kBlockK / kUmmaK; ++k)
                 mma_tf32_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc,
@@ -430,10 +454,10 @@ static void choose_pixel_box(int N, int Ho, int Wo, int stats_mode, int& BW, int
   }
 }
 
-template <int BN, int STAGES, bool HALO = false>
+template <int BN, int STAGES, bool HALO = false, bool RESW = false>
 static int launch_fprop(const CUtensorMap& mx, const CUtensorMap& mw, const CUtensorMap& my,
                         const ConvGeom& g, float* stats, int sm_count, cudaStream_t stream) {
-  using L = SmemLayout<BN, STAGES, HALO>;
+  using L = SmemLayout<BN, STAGES, HALO, RESW>;
   constexpr int smem_bytes = L::kTotal + 1024;      // + alignment slack
   // the opt-in shared-memory size is a per-device attribute of the kernel: one process may
   // drive several GPUs (single-process GPipe), so remember it per device
@@ -442,7 +466,7 @@ static int launch_fprop(const CUtensorMap& mx, const CUtensorMap& mw, const CUte
   cudaGetDevice(&dev_);
   if (dev_ < 0 || dev_ >= 64) dev_ = 0;
   bool& configured = configured_on[dev_];
-  auto kern = conv_fprop_tf32_kernel<BN, STAGES, HALO>;
+  auto kern = conv_fprop_tf32_kernel<BN, STAGES, HALO, RESW>;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          smem_bytes);
@@ -583,7 +607,13 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
       return set_error("conv_fprop: tensor map for Y failed");
   }
   int rc;
-  if (halo) {
+  bool resident = halo && g.tiles_k == 1 &&
+                  static_cast<long>(R) * S * g.c_blocks * BN * kBlockKBytes <= kResidentWBytes;
+  if (const char* env = getenv("TGB_FPROP_RESW")) resident = resident && atoi(env) != 0;
+  if (halo && resident) {
+    rc = BN == 64 ? launch_fprop<64, 2, true, true>(mx, mw, my, g, stats, sms, stream)
+                  : launch_fprop<32, 2, true, true>(mx, mw, my, g, stats, sms, stream);
+  } else if (halo) {
     rc = BN == 64 ? launch_fprop<64, 2, true>(mx, mw, my, g, stats, sms, stream)
                   : launch_fprop<32, 3, true>(mx, mw, my, g, stats, sms, stream);
   } else

@@ -347,7 +347,10 @@ int main(int argc, char** argv) {
   for (auto& c : halo_cases) {
     if (only && strcmp(only, c.name) && strcmp(only, "all") && strcmp(only, "halo")) continue;
     setenv("TGB_FPROP_HALO", "2", 1);
-    fails += run_conv_case(c, true, 0);
+    fails += run_conv_case(c, true, 0);           // filter bank resident in smem where it fits
+    setenv("TGB_FPROP_RESW", "0", 1);
+    fails += run_conv_case(c, true, 0);           // weights streamed with every stage
+    unsetenv("TGB_FPROP_RESW");
     unsetenv("TGB_FPROP_HALO");
   }
   ConvCase perf[] = {
