@@ -46,21 +46,33 @@ EXPERIMENTS = {
         4: dict(batch=1152, chunks=32, balance=[3, 6, 7, 8]),
         8: dict(batch=1280, chunks=32, balance=[2, 2, 2, 3, 3, 4, 4, 4]),
     },
+    # reference benchmarks/resnet101-speed/main.py:30-67
+    'resnet101': {
+        1: dict(batch=220, chunks=2, balance=[370]),
+        2: dict(batch=25000, chunks=1667, balance=[135, 235]),
+        4: dict(batch=5632, chunks=256, balance=[44, 92, 124, 110]),
+        8: dict(batch=5400, chunks=150, balance=[26, 22, 33, 44, 44, 66, 66, 69]),
+    },
 }
 # Reference's published P40 numbers for the same experiments.
 PUBLISHED = {'unet': {1: 24.456, 2: 35.502, 4: 67.042, 8: 88.497},
-             'amoebanetd': {2: 47.386, 4: 72.412, 8: 132.413}}
+             'amoebanetd': {2: 47.386, 4: 72.412, 8: 132.413},
+             'resnet101': {1: 81.796, 2: 135.539, 4: 265.958, 8: 411.662}}
 INPUT_HW = 192
 MODEL_INFO = {'unet': dict(hw=192, name='U-Net (B=5,C=64) 241 layers 232.7M params',
                            metric='U-Net(5,64)', loss='bce_with_logits'),
               'amoebanetd': dict(hw=224, name='AmoebaNet-D (L=18,D=256) 24 layers 122.5M params',
-                                 metric='AmoebaNet-D(18,256)', loss='cross_entropy')}
+                                 metric='AmoebaNet-D(18,256)', loss='cross_entropy'),
+              'resnet101': dict(hw=224, name='ResNet-101 370 layers 44.5M params',
+                                metric='ResNet-101', loss='cross_entropy')}
 
 
 def build_model(builders, name):
     if name == 'unet':
         return builders['unet'](depth=5, num_convs=5, base_channels=64, input_channels=3,
                                 output_channels=1)
+    if name == 'resnet101':
+        return builders['resnet101'](num_classes=1000)
     return builders['amoebanetd'](num_classes=1000, num_layers=18, num_filters=256)
 
 
@@ -213,12 +225,12 @@ def run_ours(args):
 
     from torchgpipe_b200 import GPipe
     from torchgpipe_b200 import ops
-    from torchgpipe_b200.models import amoebanetd, unet
+    from torchgpipe_b200.models import amoebanetd, resnet101, unet
     info = MODEL_INFO[args.model]
     hw = info['hw']
 
     torch.manual_seed(0)
-    model = build_model(dict(unet=unet, amoebanetd=amoebanetd), args.model)
+    model = build_model(dict(unet=unet, amoebanetd=amoebanetd, resnet101=resnet101), args.model)
     if not args.no_kernels:
         model = ops.convert_to_sm100(model)
 
@@ -388,6 +400,7 @@ def run_reference(args):
     assert os.path.realpath(torchgpipe.__file__).startswith(os.path.realpath(ref_root))
     from unet import unet  # reference model builders (benchmarks/models/*)
     from amoebanet import amoebanetd
+    from resnet import resnet101
     hw = MODEL_INFO[args.model]['hw']
 
     n = args.gpus
@@ -405,7 +418,8 @@ def run_reference(args):
 
     if driver:
         torch.manual_seed(0)
-        model = build_model(dict(unet=unet, amoebanetd=amoebanetd), args.model)
+        model = build_model(dict(unet=unet, amoebanetd=amoebanetd, resnet101=resnet101),
+                            args.model)
         devices = [torch.device('cuda', k) for k in range(n)]
         pipe = GPipe(model, balance, devices=devices, chunks=chunks)   # checkpoint default
         opt = SGD(pipe.parameters(), lr=0.1)
@@ -517,8 +531,8 @@ def main():
     p.add_argument('--steps', type=int, default=5)
     p.add_argument('--warmup', type=int, default=3)
     p.add_argument('--impl', choices=['ours', 'reference'], default='ours')
-    p.add_argument('--model', choices=['unet', 'amoebanetd'], default='unet',
-                   help='unet (default, headline) or amoebanetd (N in 2,4,8)')
+    p.add_argument('--model', choices=['unet', 'amoebanetd', 'resnet101'], default='unet',
+                   help='unet (default, headline), amoebanetd (N in 2,4,8) or resnet101')
     p.add_argument('--no-graphs', action='store_true',
                    help='ours arm, N>1: issue stage kernels eagerly instead of replaying CUDA graphs')
     p.add_argument('--no-kernels', action='store_true',
