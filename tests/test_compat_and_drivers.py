@@ -95,3 +95,42 @@ def test_accuracy_driver_smoke_on_cpu():
     assert out.returncode == 0, out.stderr[-2000:]
     rec = json.loads(out.stdout.strip().splitlines()[-1])
     assert rec['experiment'] == 'gpipe-256' and rec['epoch'] == 1
+
+
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize('experiment', ['baseline', 'dep-str-ptl'])
+def test_timeline_ablation_driver_smoke_on_cpu(experiment):
+    out = subprocess.run([sys.executable, os.path.join(ROOT, 'benchmarks', 'timeline.py'),
+                          experiment, '--smoke', '--devices', 'cpu,cpu,cpu,cpu', '--steps', '1',
+                          '--warmup', '0'], capture_output=True, text=True, timeout=280,
+                         cwd=os.path.join(ROOT, 'benchmarks'))
+    assert out.returncode == 0, out.stderr[-2000:]
+    rec = json.loads(out.stdout.strip().splitlines()[-1])
+    assert rec['benchmark'] == 'unet-timeline' and rec['samples_per_s'] > 0
+    assert rec['portals'] == (experiment == 'dep-str-ptl')
+
+
+@pytest.mark.timeout(300)
+def test_memory_driver_smoke_on_cpu():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, 'benchmarks', 'memory.py'), 'unet',
+                          'pipeline-2', '--smoke', '--devices', 'cpu,cpu'], capture_output=True,
+                         text=True, timeout=280, cwd=os.path.join(ROOT, 'benchmarks'))
+    assert out.returncode == 0, out.stderr[-2000:]
+    rec = json.loads(out.stdout.strip().splitlines()[-1])
+    assert rec['benchmark'] == 'unet-memory' and rec['parameters'] > 0
+
+
+def test_bench_experiment_tables_match_the_reference_configs():
+    sys.path.insert(0, ROOT)
+    import bench
+    # reference benchmarks/{unet,amoebanetd,resnet101}-speed/main.py
+    assert bench.EXPERIMENTS['unet'][8] == dict(batch=640, chunks=40,
+                                                balance=[16, 27, 31, 44, 22, 57, 27, 17])
+    assert bench.EXPERIMENTS['amoebanetd'][8] == dict(batch=1280, chunks=32,
+                                                      balance=[2, 2, 2, 3, 3, 4, 4, 4])
+    assert bench.EXPERIMENTS['resnet101'][4] == dict(batch=5632, chunks=256,
+                                                     balance=[44, 92, 124, 110])
+    for model, sizes in (('unet', 241), ('amoebanetd', 24), ('resnet101', 370)):
+        for cfg in bench.EXPERIMENTS[model].values():
+            assert sum(cfg['balance']) == sizes
+            assert cfg['batch'] % cfg['chunks'] == 0 or model == 'resnet101'
