@@ -139,3 +139,19 @@ def test_tuple_wait_orders_every_member(cuda_sleep):
     y.mean().backward()
     assert torch.isclose(b.grad.norm().cpu(), torch.tensor(5.000), atol=1e-2) or True
     assert torch.allclose(b.grad, torch.full_like(b.grad, 2.0 / y.numel()))
+
+
+def test_nvtx_annotations_are_noops_unless_enabled_and_cuda_is_present():
+    from torchgpipe_b200.utils import nvtx
+    assert not nvtx.enabled() or torch.cuda.is_available()
+    with nvtx.annotate('fwd mb0 stage0'):
+        pass
+    nvtx.enable(True)
+    try:
+        assert nvtx.enabled() == torch.cuda.is_available()
+        # pipelines still run with the flag on (ranges are only pushed when CUDA exists)
+        model = GPipe(nn.Sequential(nn.Linear(2, 2), nn.ReLU()), [1, 1], devices=['cpu', 'cpu'],
+                      chunks=2, checkpoint='always')
+        model(torch.rand(4, 2)).sum().backward()
+    finally:
+        nvtx.enable(False)

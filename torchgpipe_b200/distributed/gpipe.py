@@ -38,6 +38,7 @@ from torchgpipe_b200.skip.layout import inspect_skip_layout
 from torchgpipe_b200.skip.namespace import Namespace
 from torchgpipe_b200.skip.skippable import Skippable, verify_skippables
 from torchgpipe_b200.skip.tracker import SkipTracker, use_skip_tracker
+from torchgpipe_b200.utils import nvtx
 
 __all__ = ['DistributedGPipe', 'DistributedGPipeDataLoader', 'get_module_partition']
 
@@ -381,7 +382,8 @@ class DistributedGPipe:
             if self.cuda_graphs:
                 staged = self._graphed_stage(len(boundary), atomic_in, flight)
                 flight.staged = staged
-                produced, flight.rng = staged.forward(leaves)
+                with nvtx.annotate(f'fwd mb{mb} stage{self.rank}'):
+                    produced, flight.rng = staged.forward(leaves)
                 flight.n_outputs, flight.atomic = staged.meta['n_outputs'], staged.meta['atomic']
                 if self.is_last and grad_mode:
                     # the caller differentiates its loss w.r.t. these leaves; backward() feeds
@@ -390,12 +392,14 @@ class DistributedGPipe:
                         if y.is_floating_point():
                             y.requires_grad_()
             elif mb < stop:
-                chk = Checkpointing(function, Batch(leaves))
-                out_batch = chk.checkpoint()
-                chk.recompute(out_batch)
-                produced = tuple(out_batch)
+                with nvtx.annotate(f'fwd mb{mb} stage{self.rank} (checkpointed)'):
+                    chk = Checkpointing(function, Batch(leaves))
+                    out_batch = chk.checkpoint()
+                    chk.recompute(out_batch)
+                    produced = tuple(out_batch)
             else:
-                produced = function(leaves)
+                with nvtx.annotate(f'fwd mb{mb} stage{self.rank}'):
+                    produced = function(leaves)
 
             if t0 is not None:
                 self._marks.append(('fwd', t0, t1, self._mark()))
@@ -468,7 +472,8 @@ class DistributedGPipe:
                     grads.append(to(self.device, g))
 
             if roots:
-                torch.autograd.backward(roots, grads)
+                with nvtx.annotate(f'bwd mb{mb} stage{self.rank}'):
+                    torch.autograd.backward(roots, grads)
 
             leaves = flight.leaves
             if not self.is_first:
@@ -527,7 +532,8 @@ class DistributedGPipe:
             gouts.append(to(self.device, g))
         t1 = self._mark()
 
-        gin = flight.staged.backward(flight.leaves, flight.rng, gouts)
+        with nvtx.annotate(f'bwd mb{mb} stage{self.rank}'):
+            gin = flight.staged.backward(flight.leaves, flight.rng, gouts)
         if t0 is not None:
             self._marks.append(('bwd', t0, t1, self._mark()))
 

@@ -40,6 +40,7 @@ from torchgpipe_b200.runtime.streams import AbstractStream, current_stream, use_
 from torchgpipe_b200.runtime.timeline import Timeline
 from torchgpipe_b200.skip.layout import SkipLayout, inspect_skip_layout
 from torchgpipe_b200.skip.tracker import SkipTrackerThroughPotals, use_skip_tracker
+from torchgpipe_b200.utils import nvtx
 
 __all__ = ['Pipeline', 'clock_cycles', 'depend', 'copy', 'wait']
 
@@ -187,6 +188,18 @@ class Pipeline:
                     return batch.call(partition)
 
             finalize = None
+
+        if nvtx.enabled():
+            plain_run, plain_finalize = run, finalize
+
+            def run() -> Batch:                                     # type: ignore[no-redef]
+                with nvtx.annotate(f'fwd mb{i} stage{j}'):
+                    return plain_run()
+
+            if plain_finalize is not None:
+                def finalize(b: Batch) -> None:                     # type: ignore[no-redef,misc]
+                    with nvtx.annotate(f'arm recompute mb{i} stage{j}'):
+                        plain_finalize(b)
 
         if timeline is None:
             return Task(stream, compute=run, finalize=finalize)
