@@ -21,7 +21,7 @@ Contract: reference ``torchgpipe/checkpoint.py:1-308``.
 from collections import deque
 from contextlib import contextmanager
 import threading
-from typing import Any, Callable, Deque, Generator, List, Optional, Tuple, Union
+from typing import Callable, Deque, Generator, List, Optional, Tuple, Union
 
 import torch
 from torch import Tensor

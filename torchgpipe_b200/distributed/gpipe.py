@@ -27,7 +27,7 @@ from torch import Tensor, nn
 
 from torchgpipe_b200 import microbatch
 from torchgpipe_b200.batchnorm import DeferredBatchNorm
-from torchgpipe_b200.checkpoint import Checkpointing, is_recomputing
+from torchgpipe_b200.checkpoint import Checkpointing
 from torchgpipe_b200.distributed import context
 from torchgpipe_b200.distributed.transport import ChannelTransport, Transport
 from torchgpipe_b200.distributed.utils import to

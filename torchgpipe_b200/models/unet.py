@@ -8,7 +8,7 @@ per level; a final 1x1 conv. (5, 64) has 241 layers / 232.7 M parameters.
 Structure and names follow reference ``benchmarks/models/unet/__init__.py:20-148``.
 """
 from collections import OrderedDict
-from typing import Dict, List
+from typing import Dict
 
 import torch
 from torch import Tensor, nn
