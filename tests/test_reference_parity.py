@@ -141,3 +141,64 @@ def test_sequential_state_dict_moves_a_reference_checkpoint_to_another_balance(t
     other.eval()
     x = ref['x']
     assert torch.allclose(first(x), other(x), atol=1e-6)
+
+
+_PURE_DRIVER = r'''
+import sys, json, random, signal
+sys.path.insert(0, sys.argv[1])
+from torchgpipe.balance import blockpartition
+from torchgpipe.pipeline import clock_cycles
+random.seed(11)
+
+class Hang(Exception):
+    pass
+
+def on_alarm(*args):
+    raise Hang()
+
+signal.signal(signal.SIGALRM, on_alarm)
+cases = []
+for _ in range(300):
+    n = random.randint(1, 14)
+    seq = [random.choice([1, 1, 2, 3, 5, 8, 13, 0.5, 2.25]) for _ in range(n)]
+    k = random.randint(1, n)
+    signal.alarm(2)
+    try:
+        blocks = blockpartition.solve(seq, k)
+    except Hang:
+        blocks = None             # the reference's sliding loop never terminates on this input
+    finally:
+        signal.alarm(0)
+    cases.append((seq, k, blocks))
+clocks = {f'{m},{n}': [list(map(list, s)) for s in clock_cycles(m, n)]
+          for m in range(1, 7) for n in range(1, 6)}
+json.dump({'cases': cases, 'clocks': clocks}, open(sys.argv[2], 'w'))
+'''
+
+
+@pytest.mark.timeout(120)
+def test_block_partition_and_clock_cycles_agree_with_the_reference(tmp_path):
+    import json
+    from torchgpipe_b200.balance import blockpartition
+    from torchgpipe_b200.runtime.schedule import clock_cycles
+    script = tmp_path / 'pure_driver.py'
+    script.write_text(_PURE_DRIVER)
+    out = tmp_path / 'pure.json'
+    env = {k: v for k, v in os.environ.items() if k != 'PYTHONPATH'}
+    done = subprocess.run([sys.executable, str(script), REF, str(out)], capture_output=True,
+                          text=True, timeout=100, env=env, cwd=str(tmp_path))
+    assert done.returncode == 0, done.stderr[-3000:]
+    ref = json.load(open(out))
+    hangs = 0
+    for seq, k, blocks in ref['cases']:
+        mine = blockpartition.solve(seq, k)
+        if blocks is None:
+            # own solver must still answer with k non-empty contiguous blocks
+            hangs += 1
+            assert len(mine) == k and all(mine) and sum(mine, []) == seq, (seq, k)
+        else:
+            assert mine == blocks, (seq, k)
+    assert hangs < len(ref['cases']) // 10
+    for key, schedule in ref['clocks'].items():
+        m, n = map(int, key.split(','))
+        assert [[list(cell) for cell in tick] for tick in clock_cycles(m, n)] == schedule, key

@@ -40,6 +40,21 @@ def solve(sequence: List[int], partitions: int = 1) -> List[List[int]]:
         begins = [0] + ends[:-1]
         return [sequence[a:z] for a, z in zip(begins, ends)]
 
+    def spread_of() -> float:
+        ws = [weight_of(b) for b in range(partitions)]
+        return max(ws) - min(ws)
+
+    def non_empty() -> bool:
+        begins = [0] + ends[:-1]
+        return all(a < z for a, z in zip(begins, ends))
+
+    # The sliding procedure can cycle, or push a boundary past an emptied block, on some inputs
+    # (the reference then never returns, e.g. solve([8,2,8,3,2,13,2,5,2,2,3,13], 10)): remember
+    # the states seen and, on a repeat or an inconsistent state, answer with the most even state
+    # without an empty block that was visited.
+    seen = set()
+    best_ends, best_spread = list(ends), spread_of()
+
     while True:
         # Heaviest block (ties -> highest index), as in the paper's step (1).
         heavy_weight, heavy = max((weight_of(b), b) for b in range(partitions))
@@ -48,6 +63,17 @@ def solve(sequence: List[int], partitions: int = 1) -> List[List[int]]:
             light_weight, light = min((weight_of(b), b) for b in range(partitions))
             if heavy_weight <= light_weight + 1:
                 return blocks()
+
+            state = (tuple(ends), heavy, heavy_weight)
+            consistent = all(0 <= z <= n for z in ends)
+            if state in seen or not consistent:
+                ends[:] = best_ends
+                return blocks()
+            seen.add(state)
+            if non_empty():
+                spread = spread_of()
+                if spread < best_spread or not _all_non_empty(best_ends):
+                    best_ends, best_spread = list(ends), spread
 
             if heavy < light:
                 # Give the last element of the block left of `light` to `light`.
@@ -60,3 +86,8 @@ def solve(sequence: List[int], partitions: int = 1) -> List[List[int]]:
 
             if neighbour == heavy:
                 break   # the heaviest block changed: re-evaluate from step (1)
+
+
+def _all_non_empty(ends: List[int]) -> bool:
+    begins = [0] + list(ends[:-1])
+    return all(a < z for a, z in zip(begins, ends))
