@@ -202,3 +202,127 @@ def test_block_partition_and_clock_cycles_agree_with_the_reference(tmp_path):
     for key, schedule in ref['clocks'].items():
         m, n = map(int, key.split(','))
         assert [[list(cell) for cell in tick] for tick in clock_cycles(m, n)] == schedule, key
+
+
+# Each snippet must raise; the reference and this package have to agree on the exception type
+# and (modulo the package name) on the message. (Deliberate difference, not listed: a 2-D input
+# to DeferredBatchNorm raises here - the reference defines the check but never calls it.)
+_ERROR_SNIPPETS = [
+    "GPipe(nn.Sequential(nn.Linear(1, 1)))",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[2], devices=['cpu'])",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[0, 1], devices=['cpu', 'cpu'])",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[-1, 2], devices=['cpu', 'cpu'])",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[1], devices=['cpu'], chunks=0)",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[1], devices=['cpu'], checkpoint='sometimes')",
+    "GPipe(nn.Linear(1, 1), balance=[1], devices=['cpu'])",
+    "GPipe(nn.Sequential(shared, shared), balance=[2], devices=['cpu'])",
+    "GPipe(nn.Sequential(nn.Linear(1, 1), nn.Linear(1, 1)), balance=[1, 1], devices=['cpu'])",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[1], devices=['cpu']).cpu()",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[1], devices=['cpu']).to('cpu')",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[1], devices=['cpu'])('not a tensor')",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[1], devices=['cpu'])(torch.rand(1, 1), 2)",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[1], devices=['cpu'])[3]",
+    "balance_by_time(1, nn.Sequential(with_grad), torch.rand(1, 1), device='cpu')",
+    "blockpartition.solve([1, 2], 3)",
+    "blockpartition.solve([1, 2], 0)",
+    "verify_skippables(nn.Sequential(StashX()))",
+    "verify_skippables(nn.Sequential(PopX()))",
+    "verify_skippables(nn.Sequential(StashX(), StashX(), PopX()))",
+    "nn.Sequential(StashX(), PopX())(torch.rand(1))  if False else Bad()(torch.rand(1))",
+    "PopX()(torch.rand(1))",
+    "Undeclared()(torch.rand(1))",
+    "DeferredBatchNorm(3)(torch.rand(2, 4, 5, 5))",
+    "microbatch.check('x')",
+    "microbatch.check((torch.rand(1), 2))",
+    "microbatch.Batch((torch.rand(2),)).tensor",
+    "microbatch.Batch(torch.rand(2)).tensors",
+    "microbatch.scatter(torch.rand(0, 1), 2) and None.x",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[1], devices=['cpu']).to(torch.device('cpu'))",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[1], devices=['cpu']).to(tensor=torch.rand(1))",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[1], devices=['cpu']).cuda()",
+    "GPipe(nn.Sequential(nn.Linear(1, 1)), balance=[1], devices=['cpu']).no_such_attribute",
+    "balance_by_size(1, nn.Sequential(nn.Linear(1, 1)), torch.rand(1, 1), device='cpu')",
+    "GPipe(nn.Sequential(OrderedDict(a=shared, b=nn.Sequential(shared))), balance=[2], devices=['cpu'])",
+]
+
+_ERROR_DRIVER = r'''
+import sys, json
+if sys.argv[1] != '-':
+    sys.path.insert(0, sys.argv[1])
+    pkg = 'torchgpipe'
+else:
+    sys.path.insert(0, sys.argv[3])
+    pkg = 'torchgpipe_b200'
+import importlib, torch
+from torch import nn
+mod = importlib.import_module(pkg)
+GPipe = mod.GPipe
+balance = importlib.import_module(pkg + '.balance')
+balance_by_time = balance.balance_by_time
+blockpartition = importlib.import_module(pkg + '.balance.blockpartition')
+skip = importlib.import_module(pkg + '.skip')
+verify_skippables, skippable, stash, pop = skip.verify_skippables, skip.skippable, skip.stash, skip.pop
+
+from collections import OrderedDict
+microbatch = importlib.import_module(pkg + '.microbatch')
+DeferredBatchNorm = importlib.import_module(pkg + '.batchnorm').DeferredBatchNorm
+balance_by_size = balance.balance_by_size
+
+shared = nn.Linear(1, 1)
+with_grad = nn.Linear(1, 1)
+with_grad.weight.grad = torch.zeros_like(with_grad.weight)
+
+@skippable(stash=['x'])
+class StashX(nn.Module):
+    def forward(self, t):
+        yield stash('x', t)
+        return t
+
+@skippable(pop=['x'])
+class PopX(nn.Module):
+    def forward(self, t):
+        x = yield pop('x')
+        return t + x
+
+@skippable(stash=['x'])
+class Bad(nn.Module):          # declares a stash it never performs
+    def forward(self, t):
+        return t
+
+@skippable()
+class Undeclared(nn.Module):   # stashes a name it did not declare
+    def forward(self, t):
+        yield stash('y', t)
+        return t
+
+out = []
+for snippet in json.loads(sys.argv[2]):
+    try:
+        eval(snippet)
+        out.append(['no error', ''])
+    except Exception as exc:
+        out.append([type(exc).__name__, str(exc).replace('torchgpipe_b200', 'torchgpipe')])
+print('RESULT' + json.dumps(out))
+'''
+
+
+@pytest.mark.timeout(200)
+def test_error_types_and_messages_agree_with_the_reference(tmp_path):
+    import json
+    script = tmp_path / 'err_driver.py'
+    script.write_text(_ERROR_DRIVER)
+    env = {k: v for k, v in os.environ.items() if k != 'PYTHONPATH'}
+
+    def run(first):
+        done = subprocess.run([sys.executable, str(script), first, json.dumps(_ERROR_SNIPPETS),
+                               ROOT], capture_output=True, text=True, timeout=150, env=env,
+                              cwd=str(tmp_path))
+        assert done.returncode == 0, done.stderr[-3000:]
+        line = [l for l in done.stdout.splitlines() if l.startswith('RESULT')][-1]
+        return json.loads(line[len('RESULT'):])
+
+    theirs, ours = run(REF), run('-')
+    for snippet, a, b in zip(_ERROR_SNIPPETS, theirs, ours):
+        assert a[0] != 'no error', snippet
+        assert a[0] == b[0], (snippet, a, b)
+        assert a[1] == b[1], (snippet, a, b)
