@@ -326,3 +326,57 @@ def test_error_types_and_messages_agree_with_the_reference(tmp_path):
         assert a[0] != 'no error', snippet
         assert a[0] == b[0], (snippet, a, b)
         assert a[1] == b[1], (snippet, a, b)
+
+
+_DBN_DRIVER = r'''
+import sys, importlib, torch
+from torch import nn
+if sys.argv[1] != '-':
+    sys.path.insert(0, sys.argv[1]); pkg = 'torchgpipe'
+else:
+    sys.path.insert(0, sys.argv[3]); pkg = 'torchgpipe_b200'
+DBN = importlib.import_module(pkg + '.batchnorm').DeferredBatchNorm
+torch.manual_seed(3)
+results = {}
+for momentum in (0.1, None):
+    net = nn.Sequential(nn.Conv2d(3, 4, 3, padding=1), nn.BatchNorm2d(4, momentum=momentum), nn.ReLU())
+    net = DBN.convert_deferred_batch_norm(net, chunks=3)
+    x = torch.rand(9, 3, 6, 6)
+    outs = []
+    for step in range(2):                       # two mini-batches of three micro-batches
+        for chunk in x.chunk(3):
+            out = net(chunk + step)
+            out.mean().backward()
+            outs.append(out.detach())
+    net.eval()
+    results[str(momentum)] = dict(
+        outs=torch.cat(outs), eval=net(x).detach(),
+        state={k: v.clone() for k, v in net.state_dict().items()},
+        grads=[p.grad.clone() for p in net.parameters()], kind=type(net[1]).__name__)
+torch.save(results, sys.argv[2])
+'''
+
+
+@pytest.mark.timeout(200)
+def test_deferred_batch_norm_matches_the_reference(tmp_path):
+    script = tmp_path / 'dbn_driver.py'
+    script.write_text(_DBN_DRIVER)
+    env = {k: v for k, v in os.environ.items() if k != 'PYTHONPATH'}
+    got = {}
+    for tag, first in (('ref', REF), ('ours', '-')):
+        out = tmp_path / f'dbn_{tag}.pt'
+        done = subprocess.run([sys.executable, str(script), first, str(out), ROOT],
+                              capture_output=True, text=True, timeout=150, env=env,
+                              cwd=str(tmp_path))
+        assert done.returncode == 0, done.stderr[-3000:]
+        got[tag] = torch.load(out)
+    for momentum in ('0.1', 'None'):
+        a, b = got['ref'][momentum], got['ours'][momentum]
+        assert a['kind'] == b['kind'] == 'DeferredBatchNorm'
+        assert list(a['state'].keys()) == list(b['state'].keys())
+        for k in a['state']:
+            assert torch.allclose(a['state'][k].float(), b['state'][k].float(), atol=1e-6), k
+        assert torch.allclose(a['outs'], b['outs'], atol=1e-6)
+        assert torch.allclose(a['eval'], b['eval'], atol=1e-5)
+        for g, h in zip(a['grads'], b['grads']):
+            assert torch.allclose(g, h, atol=1e-6)
