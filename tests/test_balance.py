@@ -140,3 +140,26 @@ def test_balance_by_size_param_and_scale():
     sample = torch.rand(1, requires_grad=True)
     assert balance_by_size(2, model, sample, param_scale=0, device='cuda') == [2, 4]
     assert balance_by_size(2, model, sample, param_scale=100, device='cuda') == [4, 2]
+
+
+def test_optimal_solver_minimises_the_heaviest_block():
+    import itertools
+    import random
+    from torchgpipe_b200.balance import balance_cost, blockpartition
+    random.seed(5)
+    for _ in range(60):
+        n = random.randint(1, 9)
+        seq = [random.choice([1, 2, 3, 5, 8, 0.5]) for _ in range(n)]
+        k = random.randint(1, n)
+        blocks = blockpartition.solve_optimal(seq, k)
+        assert len(blocks) == k and all(blocks) and sum(blocks, []) == seq
+        # brute force over all cut positions
+        best = min(max(sum(seq[a:z]) for a, z in zip((0,) + cuts, cuts + (n,)))
+                   for cuts in itertools.combinations(range(1, n), k - 1))
+        assert max(map(sum, blocks)) == pytest.approx(best)
+    # the input on which the reference's heuristic never terminates
+    hard = [8, 2, 8, 3, 2, 13, 2, 5, 2, 2, 3, 13]
+    assert max(map(sum, blockpartition.solve_optimal(hard, 10))) == 13
+    assert balance_cost([1, 1, 1, 10], 2, solver='optimal') == [3, 1]
+    with pytest.raises(ValueError):
+        balance_cost([1, 2], 1, solver='greedy')

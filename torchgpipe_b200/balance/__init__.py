@@ -30,9 +30,16 @@ Tensors = Tuple[Tensor, ...]
 TensorOrTensors = Union[Tensor, Tensors]
 
 
-def balance_cost(cost: List[int], partitions: int) -> List[int]:
-    """Number of layers per stage for the given per-layer costs."""
-    return [len(block) for block in blockpartition.solve(cost, partitions)]
+def balance_cost(cost: List[int], partitions: int, solver: str = 'reference') -> List[int]:
+    """Number of layers per stage for the given per-layer costs.
+
+    ``solver='reference'``: the reference's sliding heuristic (:func:`blockpartition.solve`);
+    ``solver='optimal'``: exact min-max split (:func:`blockpartition.solve_optimal`).
+    """
+    if solver not in ('reference', 'optimal'):
+        raise ValueError("solver is not one of 'reference' or 'optimal'")
+    solve = blockpartition.solve if solver == 'reference' else blockpartition.solve_optimal
+    return [len(block) for block in solve(cost, partitions)]
 
 
 def balance_by_time(partitions: int,
@@ -41,6 +48,7 @@ def balance_by_time(partitions: int,
                     *,
                     timeout: float = 1.0,
                     device: Device = torch.device('cuda'),
+                    solver: str = 'reference',
                     ) -> List[int]:
     """Balances by measured forward+backward time of each layer.
 
@@ -54,12 +62,14 @@ def balance_by_time(partitions: int,
         device: CPU or CUDA device to profile on (default: current CUDA device).
             On CUDA, layers are timed with CUDA events on the device, not with
             the host clock.
+        solver: ``'reference'`` (default, the reference's heuristic) or ``'optimal'``
+            (exact min-max contiguous split; never yields an empty stage).
 
     Returns:
         list of layer counts, one per stage, for ``GPipe(balance=...)``.
     """
     times = profile_times(module, sample, timeout, torch.device(device))
-    return balance_cost(times, partitions)
+    return balance_cost(times, partitions, solver)
 
 
 def balance_by_size(partitions: int,
@@ -69,6 +79,7 @@ def balance_by_size(partitions: int,
                     chunks: int = 1,
                     param_scale: float = 2.0,
                     device: Device = torch.device('cuda'),
+                    solver: str = 'reference',
                     ) -> List[int]:
     """Balances by CUDA memory each layer needs for training.
 
@@ -95,9 +106,10 @@ def balance_by_size(partitions: int,
         chunks: number of micro-batches used in training (default 1).
         param_scale: copies of the parameters held during training (default 2.0).
         device: CUDA device to profile on (CUDA only).
+        solver: as in :func:`balance_by_time`.
 
     Returns:
         list of layer counts, one per stage.
     """
     sizes = profile_sizes(module, input, chunks, param_scale, torch.device(device))
-    return balance_cost(sizes, partitions)
+    return balance_cost(sizes, partitions, solver)

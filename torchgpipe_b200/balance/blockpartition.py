@@ -10,7 +10,7 @@ stage balancing. Contract: reference ``torchgpipe/balance/blockpartition.py:11-8
 """
 from typing import List
 
-__all__ = ['solve']
+__all__ = ['solve', 'solve_optimal']
 
 
 def solve(sequence: List[int], partitions: int = 1) -> List[List[int]]:
@@ -91,3 +91,51 @@ def solve(sequence: List[int], partitions: int = 1) -> List[List[int]]:
 def _all_non_empty(ends: List[int]) -> bool:
     begins = [0] + list(ends[:-1])
     return all(a < z for a, z in zip(begins, ends))
+
+
+def solve_optimal(sequence: List[float], partitions: int = 1) -> List[List[float]]:
+    """Contiguous split of ``sequence`` into ``partitions`` non-empty blocks that minimises the
+    heaviest block (the pipeline's bottleneck stage), ties broken by the smallest sum of squared
+    block sums (evens out the other stages). Exact dynamic programme, O(partitions * n^2).
+
+    Not in the reference: :func:`solve` (Barany & Grinberg's sliding heuristic) stays the default
+    of the balancers for parity; pass ``solver='optimal'`` to ``balance_by_time`` /
+    ``balance_by_size`` to use this one.
+    """
+    if partitions < 1:
+        raise ValueError(f'partitions must be a positive integer ({partitions} < 1)')
+    n = len(sequence)
+    if n < partitions:
+        raise ValueError(f'sequence is shorter than intended partitions ({n} < {partitions})')
+
+    prefix = [0.0]
+    for x in sequence:
+        prefix.append(prefix[-1] + x)
+
+    def block(a: int, z: int) -> float:
+        return prefix[z] - prefix[a]
+
+    inf = (float('inf'), float('inf'))
+    # best[k][i]: (bottleneck, sum of squares) of the best split of the first i items into k blocks
+    best = [[inf] * (n + 1) for _ in range(partitions + 1)]
+    cut = [[0] * (n + 1) for _ in range(partitions + 1)]
+    best[0][0] = (0.0, 0.0)
+    for k in range(1, partitions + 1):
+        for i in range(k, n - (partitions - k) + 1):
+            for j in range(k - 1, i):
+                head = best[k - 1][j]
+                if head == inf:
+                    continue
+                last = block(j, i)
+                cand = (max(head[0], last), head[1] + last * last)
+                if cand < best[k][i]:
+                    best[k][i] = cand
+                    cut[k][i] = j
+    ends = []
+    i = n
+    for k in range(partitions, 0, -1):
+        ends.append(i)
+        i = cut[k][i]
+    ends.reverse()
+    begins = [0] + ends[:-1]
+    return [sequence[a:z] for a, z in zip(begins, ends)]
