@@ -380,3 +380,74 @@ def test_deferred_batch_norm_matches_the_reference(tmp_path):
         assert torch.allclose(a['eval'], b['eval'], atol=1e-5)
         for g, h in zip(a['grads'], b['grads']):
             assert torch.allclose(g, h, atol=1e-6)
+
+
+# The reference's multi-process mode, run as two threads in one process with its RPC send
+# replaced by a direct call (what its own test-suite does with mock.patch), against this
+# package's DistributedGPipe on the in-process channel transport.
+_DIST_DRIVER = r'''
+import sys, importlib, threading, torch
+from torch import nn
+ref = sys.argv[1] != '-'
+sys.path.insert(0, sys.argv[1] if ref else sys.argv[3])
+pkg = 'torchgpipe' if ref else 'torchgpipe_b200'
+context = importlib.import_module(pkg + '.distributed.context')
+gp = importlib.import_module(pkg + '.distributed.gpipe')
+DistributedGPipe = gp.DistributedGPipe
+if ref:
+    def direct_put(name, id, values, backward=False):
+        (context.put_backward if backward else context.put_forward)(name, id, values)
+    DistributedGPipe._put = staticmethod(direct_put)
+
+torch.manual_seed(5)
+model = nn.Sequential(nn.Linear(4, 8), nn.Tanh(), nn.Linear(8, 8), nn.Tanh(), nn.Linear(8, 2))
+x, balance, chunks = torch.rand(6, 4), [2, 3], 3
+workers = {0: 'w0', 1: 'w1'}
+losses_out, errors = [], []
+
+def run(rank):
+    try:
+        with context.worker(workers[rank], chunks):
+            barrier.wait()
+            pipe = DistributedGPipe(model, rank, workers, balance, chunks,
+                                    device=torch.device('cpu'))
+            outs = pipe.forward(x if rank == 0 else None)
+            if rank == 1:
+                losses = [o.square().sum() / 6 for o in outs]
+                losses_out.extend(l.detach() for l in losses)
+                pipe.backward(losses)
+            else:
+                pipe.backward(None)
+            barrier.wait()
+    except Exception as exc:
+        errors.append(repr(exc))
+        barrier.abort()
+
+barrier = threading.Barrier(2)
+threads = [threading.Thread(target=run, args=(r,)) for r in (0, 1)]
+[t.start() for t in threads]
+[t.join(60) for t in threads]
+assert not errors, errors
+torch.save({'grads': [p.grad.clone() for p in model.parameters()],
+            'losses': torch.stack(losses_out)}, sys.argv[2])
+'''
+
+
+@pytest.mark.timeout(200)
+def test_distributed_mode_matches_the_reference_distributed_mode(tmp_path):
+    if not os.path.isdir(os.path.join(REF, 'torchgpipe', 'distributed')):
+        pytest.skip('reference distributed package not staged')
+    script = tmp_path / 'dist_driver.py'
+    script.write_text(_DIST_DRIVER)
+    env = {k: v for k, v in os.environ.items() if k != 'PYTHONPATH'}
+    got = {}
+    for tag, first in (('ref', REF), ('ours', '-')):
+        out = tmp_path / f'dist_{tag}.pt'
+        done = subprocess.run([sys.executable, str(script), first, str(out), ROOT],
+                              capture_output=True, text=True, timeout=150, env=env,
+                              cwd=str(tmp_path))
+        assert done.returncode == 0, done.stderr[-3000:]
+        got[tag] = torch.load(out)
+    assert torch.allclose(got['ref']['losses'], got['ours']['losses'], atol=1e-6)
+    for a, b in zip(got['ref']['grads'], got['ours']['grads']):
+        assert torch.allclose(a, b, atol=1e-6)
