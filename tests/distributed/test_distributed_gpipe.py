@@ -266,3 +266,63 @@ def test_gloo_multiprocess_matches_plain_model(checkpoint, world, balance):
     got = sum((ret[r] for r in range(world)), [])
     for g, r in zip(got, ref_grads):
         assert torch.allclose(g, 2 * r, atol=1e-5)     # two accumulated steps
+
+
+def _state_worker(rank, world, port, balance, ret):
+    import torch.distributed as dist
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        model = _full_model(seed=3)
+        pipe = DistributedGPipe(model, rank, {r: f's{r}' for r in range(world)}, balance, 2,
+                                device=torch.device('cpu'))
+        with torch.no_grad():
+            for p in pipe.model().parameters():
+                p.add_(rank + 1.0)                       # every stage changes its own part
+        merged = pipe.gather_sequential_state_dict(dst=0)
+        if rank == 0:
+            ret['merged'] = merged
+        else:
+            assert merged is None
+        # restore a whole-model checkpoint: each rank takes only its own entries
+        fresh = _full_model(seed=4).state_dict()
+        pipe.load_sequential_state_dict(fresh)
+        ret[rank] = {k: v.clone() for k, v in pipe.sequential_state_dict().items()}
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_state_dict_gather_and_load_across_ranks():
+    world, balance = 2, [2, 3]
+    port = 31500 + os.getpid() % 2000
+    manager = mp.Manager()
+    ret = manager.dict()
+    mp.spawn(_state_worker, args=(world, port, balance, ret), nprocs=world, join=True)
+    plain = _full_model(seed=3)
+    want = plain.state_dict()
+    merged = ret['merged']
+    assert list(merged.keys()) == list(want.keys())          # plain nn.Sequential keys, in order
+    for k, v in want.items():
+        bump = 1.0 if int(k.split('.')[0]) < 2 else 2.0
+        assert torch.allclose(merged[k], v + bump), k
+    fresh = _full_model(seed=4).state_dict()
+    loaded = {}
+    for r in range(world):
+        loaded.update(ret[r])
+    assert set(loaded) == set(fresh)
+    for k, v in fresh.items():
+        assert torch.equal(loaded[k], v), k
+
+
+def test_load_sequential_state_dict_is_strict_about_own_entries():
+    model = _full_model()
+    pipe = DistributedGPipe(model, 0, {0: 'x0', 1: 'x1'}, [2, 3], 1)
+    state = _full_model(seed=9).state_dict()
+    del state['0.bias']
+    with pytest.raises(RuntimeError, match='0.bias'):
+        pipe.load_sequential_state_dict(state)
+    pipe.load_sequential_state_dict(state, strict=False)
+    assert torch.equal(pipe.model()[0].weight, state['0.weight'])

@@ -297,6 +297,38 @@ class DistributedGPipe:
         """This rank's stage (give its parameters to the local optimiser)."""
         return self.module
 
+    # -- model persistence -------------------------------------------------------
+    def sequential_state_dict(self) -> 'OrderedDict[str, Tensor]':
+        """This stage's parameters and buffers under the keys of the un-partitioned
+        ``nn.Sequential`` (stages keep the original child names, so the union over all ranks IS
+        the plain model's ``state_dict``). The reference keeps per-process partitions and has no
+        way to put them back together."""
+        return self.module.state_dict()
+
+    def gather_sequential_state_dict(self, dst: int = 0, group: Any = None,
+                                     ) -> Optional['OrderedDict[str, Tensor]']:
+        """Collects every stage's :meth:`sequential_state_dict` on rank ``dst`` (CPU tensors, in
+        stage order); returns ``None`` on the other ranks. Needs an initialised
+        ``torch.distributed`` process group; every rank of the pipeline must call it."""
+        import torch.distributed as dist
+        mine = OrderedDict((k, v.detach().cpu()) for k, v in self.module.state_dict().items())
+        me = dist.get_rank(group)
+        parts: Optional[List[Any]] = [None] * dist.get_world_size(group) if me == dst else None
+        dist.gather_object((self.rank, mine), parts, dst=dst, group=group)
+        if parts is None:
+            return None
+        merged: 'OrderedDict[str, Tensor]' = OrderedDict()
+        for _, part in sorted(parts, key=lambda item: item[0]):
+            merged.update(part)
+        return merged
+
+    def load_sequential_state_dict(self, state: Dict[str, Tensor], strict: bool = True) -> Any:
+        """Loads this stage's entries out of a state dict of the whole ``nn.Sequential`` (or of
+        any superset: entries of layers owned by other stages are ignored)."""
+        names = {name for name, _ in self.module.named_children()}
+        mine = OrderedDict((k, v) for k, v in state.items() if k.split('.', 1)[0] in names)
+        return self.module.load_state_dict(mine, strict=strict)
+
     def _checkpoint_stop(self, m: int) -> int:
         if not (self.module.training and torch.is_grad_enabled()):
             return 0
