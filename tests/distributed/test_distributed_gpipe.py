@@ -326,3 +326,46 @@ def test_load_sequential_state_dict_is_strict_about_own_entries():
         pipe.load_sequential_state_dict(state)
     pipe.load_sequential_state_dict(state, strict=False)
     assert torch.equal(pipe.model()[0].weight, state['0.weight'])
+
+
+def _shape_worker(rank, world, port, ret):
+    import torch.distributed as dist
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from torchgpipe_b200.distributed.transport import ProcessGroupTransport
+        static = ProcessGroupTransport(torch.device('cpu'))
+        dynamic = ProcessGroupTransport(torch.device('cpu'), static_shapes=False)
+        if rank == 0:
+            static.send(1, ('fwd', 0, 0), torch.ones(2, 3))
+            static.send(1, ('fwd', 0, 0), torch.ones(2, 3) * 2)        # same shape: no header
+            try:
+                static.send(1, ('fwd', 0, 0), torch.ones(4, 3))
+                ret['error'] = None
+            except ValueError as exc:
+                ret['error'] = str(exc)
+            dynamic.send(1, ('fwd', 1, 0), torch.ones(2, 3))
+            dynamic.send(1, ('fwd', 1, 0), (torch.ones(5), torch.zeros(1, 2)))
+            static.flush()
+            dynamic.flush()
+        else:
+            a = static.recv(0, ('fwd', 0, 0))
+            b = static.recv(0, ('fwd', 0, 0))
+            c = dynamic.recv(0, ('fwd', 1, 0))
+            d = dynamic.recv(0, ('fwd', 1, 0))
+            ret['got'] = (a.sum().item(), b.sum().item(), tuple(c.shape),
+                          tuple(tuple(t.shape) for t in d))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_static_shape_transport_refuses_a_changed_shape_and_dynamic_one_follows_it():
+    port = 33500 + os.getpid() % 2000
+    manager = mp.Manager()
+    ret = manager.dict()
+    mp.spawn(_shape_worker, args=(2, port, ret), nprocs=2, join=True)
+    assert ret['error'] is not None and 'static_shapes' in ret['error']
+    assert ret['got'] == (6.0, 12.0, (2, 3), ((5,), (1, 2)))

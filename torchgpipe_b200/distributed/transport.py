@@ -112,7 +112,7 @@ class ProcessGroupTransport(Transport):
         self.static_shapes = static_shapes
         self._pair_groups: Dict[Tuple[int, int], Any] = {}
         self._use_pair_groups = pair_groups
-        self._known_send: Dict[Tuple[int, Key], bool] = {}
+        self._known_send: Dict[Tuple[int, Key], Any] = {}
         self._known_recv: Dict[Tuple[int, Key], Any] = {}
         self._pending: List[Any] = []
 
@@ -198,11 +198,20 @@ class ProcessGroupTransport(Transport):
         slot = (dst, key)
         atomic = torch.is_tensor(value)
         tensors = (value,) if atomic else tuple(value)
-        if key[0] not in ('bwd', 'skip_grad') and \
-                (not self.static_shapes or slot not in self._known_send):
+        if key[0] not in ('bwd', 'skip_grad'):
             # Gradient messages never need a header: the receiver passes `like`.
-            self._pending.append(self.dist.isend(self._encode(tensors, atomic), peer, group=group))
-            self._known_send[slot] = True
+            meta = (atomic, tuple((t.dtype, tuple(t.shape)) for t in tensors))
+            known = self._known_send.get(slot)
+            if not self.static_shapes or known is None:
+                self._pending.append(
+                    self.dist.isend(self._encode(tensors, atomic), peer, group=group))
+                self._known_send[slot] = meta
+            elif known != meta:
+                # the receiver allocates from the header it cached on the first message
+                raise ValueError(
+                    f'message {key} to stage {dst} changed shape or dtype ({known[1]} -> '
+                    f'{meta[1]}) but this transport was created with static_shapes=True; use '
+                    'ProcessGroupTransport(static_shapes=False) for varying batch sizes')
         # Completed sends are dropped right away: a pending handle keeps its tensor alive, and
         # activations are large (a leaked handle per message grows memory by GBs per step).
         self._reap()
