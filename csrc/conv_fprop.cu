@@ -483,25 +483,19 @@ static int launch_fprop(const CUtensorMap& mx, const CUtensorMap& mw, const CUte
   return 0;
 }
 
-}  // namespace tgb
-
-using namespace tgb;
-
-extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, float* stats,
-                                     int N, int H, int W, int C, int K, int R, int S, int pad_h,
-                                     int pad_w, int stats_mode, cudaStream_t stream) {
-  if (C % 4 != 0 || K % 4 != 0)
-    return set_error("conv_fprop: need C %% 4 == 0 and K %% 4 == 0 (got C=%d K=%d)", C, K);
-  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) |
-       reinterpret_cast<uintptr_t>(y)) & 15)
-    return set_error("conv_fprop: tensors must be 16-byte aligned");
-  ConvGeom g;
+// Everything that is decided on the host before a launch: tile shapes, kernel variant, split of
+// the reduction. Shared by the launcher and by tgb_conv2d_fprop_plan (which lets callers and the
+// CPU test-suite see the decisions without a GPU). `stats_mode` is the effective mode (0 when no
+// statistics buffer is given).
+static int plan_fprop(int N, int H, int W, int C, int K, int R, int S, int pad_h, int pad_w,
+                      int stats_mode, ConvGeom& g, int& BN_out, bool& halo_out,
+                      bool& resident_out) {
   g.N = N; g.H = H; g.W = W; g.C = C; g.K = K;
   g.R = R; g.S = S; g.pad_h = pad_h; g.pad_w = pad_w;
   g.Ho = H + 2 * pad_h - R + 1;
   g.Wo = W + 2 * pad_w - S + 1;
   if (g.Ho <= 0 || g.Wo <= 0) return set_error("conv_fprop: empty output");
-  choose_pixel_box(N, g.Ho, g.Wo, stats ? stats_mode : 0, g.BW, g.BH, g.BNB);
+  choose_pixel_box(N, g.Ho, g.Wo, stats_mode, g.BW, g.BH, g.BNB);
   // Output-channel tile: the widest of {256,128,64,32} that wastes at most 1/8 of its columns.
   // A partial last tile is fine: weight rows past K are zero-filled by TMA and the store of
   // columns past K is clipped.
@@ -533,7 +527,7 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
   g.tiles_n = (N + g.BNB - 1) / g.BNB;
   g.tiles_k = (K + BN - 1) / BN;
   g.c_blocks = (C + kBlockK - 1) / kBlockK;
-  g.stats_mode = stats ? stats_mode : 0;
+  g.stats_mode = stats_mode;
   // Few output tiles and a long reduction (small images, many channels - e.g. 2048 ch at 6x6,
   // or any layer at a small micro-batch): split the (tap, channel-block) loop over CTAs so the
   // whole GPU works; partial sums are combined by TMA reduce-add into a zeroed Y.
@@ -569,6 +563,34 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
   }
   g.iters_per_split = (k_iters + g.splits - 1) / g.splits;
   g.splits = (k_iters + g.iters_per_split - 1) / g.iters_per_split;
+  bool resident = halo && g.tiles_k == 1 &&
+                  static_cast<long>(R) * S * g.c_blocks * BN * kBlockKBytes <= kResidentWBytes;
+  if (const char* env = getenv("TGB_FPROP_RESW")) resident = resident && atoi(env) != 0;
+  BN_out = BN;
+  halo_out = halo;
+  resident_out = resident;
+  return 0;
+}
+
+}  // namespace tgb
+
+using namespace tgb;
+
+extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, float* stats,
+                                     int N, int H, int W, int C, int K, int R, int S, int pad_h,
+                                     int pad_w, int stats_mode, cudaStream_t stream) {
+  if (C % 4 != 0 || K % 4 != 0)
+    return set_error("conv_fprop: need C %% 4 == 0 and K %% 4 == 0 (got C=%d K=%d)", C, K);
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) |
+       reinterpret_cast<uintptr_t>(y)) & 15)
+    return set_error("conv_fprop: tensors must be 16-byte aligned");
+  ConvGeom g;
+  int BN = 32;
+  bool halo = false, resident = false;
+  if (int rc = plan_fprop(N, H, W, C, K, R, S, pad_h, pad_w, stats ? stats_mode : 0, g, BN, halo,
+                          resident))
+    return rc;
+  const int sms = sm_count();
   const bool stats_after = g.splits > 1 && g.stats_mode != 0;
   const int stats_mode_req = g.stats_mode;
   if (g.splits > 1) {
@@ -607,9 +629,6 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
       return set_error("conv_fprop: tensor map for Y failed");
   }
   int rc;
-  bool resident = halo && g.tiles_k == 1 &&
-                  static_cast<long>(R) * S * g.c_blocks * BN * kBlockKBytes <= kResidentWBytes;
-  if (const char* env = getenv("TGB_FPROP_RESW")) resident = resident && atoi(env) != 0;
   if (halo && resident) {
     rc = BN == 64 ? launch_fprop<64, 2, true, true>(mx, mw, my, g, stats, sms, stream)
                   : launch_fprop<32, 2, true, true>(mx, mw, my, g, stats, sms, stream);
@@ -629,4 +648,24 @@ extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, f
                              : tgb_moments(y, stats, 1, N * g.Ho * g.Wo, K, stream);
   }
   return rc;
+}
+
+// out[16]: BN, BW, BH, BNB, tiles_w, tiles_h, tiles_n, tiles_k, splits, iters_per_split, halo,
+// resident filter bank, pipeline stages, reduction iterations per tile, Ho, Wo.
+extern "C" int tgb_conv2d_fprop_plan(int N, int H, int W, int C, int K, int R, int S, int pad_h,
+                                     int pad_w, int stats_mode, int* out) {
+  if (C % 4 != 0 || K % 4 != 0)
+    return set_error("conv_fprop: need C %% 4 == 0 and K %% 4 == 0 (got C=%d K=%d)", C, K);
+  ConvGeom g;
+  int BN = 32;
+  bool halo = false, resident = false;
+  if (int rc = plan_fprop(N, H, W, C, K, R, S, pad_h, pad_w, stats_mode, g, BN, halo, resident))
+    return rc;
+  const int stages = halo ? (resident ? 2 : (BN == 64 ? 2 : 3))
+                          : (BN == 256 ? 4 : BN == 128 ? 6 : 8);
+  const int values[16] = {BN, g.BW, g.BH, g.BNB, g.tiles_w, g.tiles_h, g.tiles_n, g.tiles_k,
+                          g.splits, g.iters_per_split, halo ? 1 : 0, resident ? 1 : 0, stages,
+                          (halo ? 1 : R * S) * g.c_blocks, g.Ho, g.Wo};
+  for (int i = 0; i < 16; ++i) out[i] = values[i];
+  return 0;
 }

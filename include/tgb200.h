@@ -133,6 +133,15 @@ int tgb_upsample2x_cat_fwd(const float* x, const float* skip, float* out, int N,
 int tgb_upsample2x_cat_bwd(const float* dout, float* dx, float* dskip, int N, int Hx, int Wx,
                            int C1, int Hs, int Ws, int C2, cudaStream_t stream);
 
+/* What tgb_conv2d_fprop_tf32 would do for a problem, without launching anything (works without a
+ * GPU: 148 SMs are assumed then). out[16] = BN, BW, BH, BNB (output tile: BN channels x a
+ * BW x BH x BNB pixel box), tiles_w, tiles_h, tiles_n, tiles_k, splits of the reduction,
+ * iterations per split, haloed-tile variant (0/1), filter bank resident in shared memory (0/1),
+ * pipeline stages, reduction iterations per tile, Ho, Wo. stats_mode as for the forward call
+ * (0 when no statistics are wanted). */
+int tgb_conv2d_fprop_plan(int N, int H, int W, int C, int K, int R, int S, int pad_h, int pad_w,
+                          int stats_mode, int* out);
+
 /* Weights of the data-gradient pass: wt[c][R-1-r][S-1-s][k] = w[k][r][s][c] (tap flip + channel
  * transpose, KRSC memory on both sides) in one coalesced pass; the dgrad of a stride-1
  * convolution is then tgb_conv2d_fprop_tf32(dy, wt). */

@@ -112,3 +112,34 @@ def test_unet_and_amoebanet_conversion_keep_keys():
         n = len(model)
         fused = ops.convert_to_sm100(model)
         assert list(fused.state_dict().keys()) == keys and len(fused) == n
+
+
+def test_forward_convolution_plans_are_pinned():
+    """Host-side decisions of the tcgen05 forward kernel (no GPU needed: 148 SMs assumed)."""
+    from torchgpipe_b200.ops import _lib
+    if _lib.load() is None:
+        pytest.skip('native library not built')
+    from torchgpipe_b200.ops.functional import conv2d_plan
+    # narrow, high-resolution layer: haloed 8x16 tiles, filter bank resident in shared memory
+    p = conv2d_plan(40, 64, 192, 192, 64)
+    assert (p['BN'], p['BW'], p['BH'], p['BNB']) == (64, 8, 16, 1)
+    assert p['halo'] and p['resident_weights'] and p['splits'] == 1 and p['stages'] == 2
+    # 256 -> 64: the filter bank (576 KB) cannot stay resident, weights stream with the stages
+    p = conv2d_plan(40, 256, 96, 96, 64)
+    assert p['halo'] and not p['resident_weights']
+    # too few tiles for the haloed variant: the per-tap kernel
+    assert not conv2d_plan(2, 64, 16, 16, 64)['halo']
+    # 12x12 images: row bands of several images fill 120 of 128 MMA rows; reduction split in 3
+    p = conv2d_plan(40, 1024, 12, 12, 1024)
+    assert (p['BN'], p['BW'], p['BH'], p['BNB']) == (256, 12, 2, 5)
+    assert not p['halo'] and p['splits'] == 3 and p['splits'] * p['iters_per_split'] >= 288
+    # per-image statistics make extra images per tile expensive: 24x24 keeps one image per tile
+    assert conv2d_plan(40, 256, 24, 24, 512, stats_mode=1)['BNB'] == 1
+    assert conv2d_plan(40, 256, 24, 24, 512, stats_mode=0)['BNB'] == 5
+    # wide layers with many tiles: no split
+    assert conv2d_plan(40, 256, 48, 48, 256)['splits'] == 1
+    # 1x1 convolution / linear layer: never haloed
+    p = conv2d_plan(40, 2048, 1, 1, 1000, 1, 1, (0, 0))
+    assert not p['halo'] and p['Ho'] == 1 and p['tiles_k'] * p['BN'] >= 1000
+    with pytest.raises(RuntimeError, match='C % 4'):
+        conv2d_plan(1, 3, 8, 8, 64)

@@ -15,7 +15,7 @@ from torchgpipe_b200.ops import _lib
 
 __all__ = ['linear', 'conv2d', 'conv2d_forward', 'instnorm_leaky', 'channel_moments', 'conv_supported',
            'refresh_dgrad_weight', 'batchnorm_act', 'maxpool2x2', 'upsample2x_cat', 'pool2d',
-           'pool_supported', 'global_avgpool', 'add_act', 'batchnorm_add_act']
+           'pool_supported', 'global_avgpool', 'add_act', 'batchnorm_add_act', 'conv2d_plan']
 
 _CL = torch.channels_last
 _c_int = ctypes.c_int
@@ -575,3 +575,23 @@ def batchnorm_add_act(y: Tensor, stats: Optional[Tensor], weight: Optional[Tenso
         stats = channel_moments(y)
     return _BatchNormAddAct.apply(y, stats, weight, bias, res, running_mean, running_var,
                                   float(eps), float(momentum), bool(relu))
+
+
+_PLAN_FIELDS = ('BN', 'BW', 'BH', 'BNB', 'tiles_w', 'tiles_h', 'tiles_n', 'tiles_k', 'splits',
+                'iters_per_split', 'halo', 'resident_weights', 'stages', 'iters_per_tile', 'Ho',
+                'Wo')
+
+
+def conv2d_plan(N: int, C: int, H: int, W: int, K: int, R: int = 3, S: int = 3,
+                padding: Tuple[int, int] = (1, 1), stats_mode: int = 0) -> dict:
+    """Host-side decisions of the forward convolution for one problem (tile shape, kernel
+    variant, split of the reduction) as a dict - no launch, no GPU needed. For tuning, for
+    explaining a layer's speed, and pinned by the CPU test-suite."""
+    out = (ctypes.c_int * 16)()
+    rc = _lib.require().tgb_conv2d_fprop_plan(_c_int(N), _c_int(H), _c_int(W), _c_int(C), _c_int(K),
+                                              _c_int(R), _c_int(S), _c_int(padding[0]),
+                                              _c_int(padding[1]), _c_int(stats_mode), out)
+    _lib.check(rc, 'tgb_conv2d_fprop_plan')
+    plan = dict(zip(_PLAN_FIELDS, list(out)))
+    plan['halo'], plan['resident_weights'] = bool(plan['halo']), bool(plan['resident_weights'])
+    return plan
