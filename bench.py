@@ -22,11 +22,21 @@ library installed under ``baseline/_ref`` driven through its own public API
 (``torchgpipe.GPipe`` in one process spanning N GPUs - its only packaged multi-GPU mode;
 under torchrun rank 0 drives it and the other ranks only join the barriers).
 
-Rank 0 prints ONE JSON line.
+Rank 0 prints ONE JSON line. ``value`` is the U-Net experiment of that N; the AmoebaNet-D
+(18,256) half of the metric (reference ``benchmarks/amoebanetd-speed/main.py:50-96``: n2m32,
+n4m32, n8m32 - it defines no 1-GPU run) is measured right after it in a child process per rank
+(own rendezvous port, so a failure there cannot take the headline down) and reported under
+``secondary``. Both arms do the same.
+
+Before anything is timed, the arm under test runs one eager step of the converted model and one
+of the plain PyTorch model (same weights, dropout off) through the same pipeline and asserts that
+the losses and the per-stage gradient norms agree (``numerics``).
 """
 import argparse
+import copy
 import json
 import os
+import socket
 import statistics
 import subprocess
 import sys
@@ -177,36 +187,181 @@ class L2Flusher:
         self.buf.zero_()
 
 
-def timed_loop(torch, dist, step_fn, steps, warmup, device, flush, world):
-    """W untimed steps, then exactly K steps between barrier+synchronize, CUDA-event timed."""
+def timed_loop(torch, dist, step_fn, steps, warmup, devices, flush, world, reduce_device):
+    """W untimed steps, then exactly K steps between barrier + synchronize on both sides.
+
+    Device time: one CUDA-event pair per participating device of this process (this arm's rank
+    owns one; the reference arm's driver rank owns all N). The end event of a device is recorded
+    once every stream of that device has drained, so work on side / communication streams is
+    inside the interval; the result is the longest interval, then the MAX over ranks. Both arms
+    are timed by this one function."""
+    def sync_all():
+        for d in devices:
+            torch.cuda.synchronize(d)
+
     for _ in range(warmup):
         step_fn()
         flush()
+    sync_all()
     if world > 1:
         dist.barrier()
-    torch.cuda.synchronize()
-    start = torch.cuda.Event(enable_timing=True)
-    end = torch.cuda.Event(enable_timing=True)
+    sync_all()
+    starts = [torch.cuda.Event(enable_timing=True) for _ in devices]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in devices]
     wall0 = time.perf_counter()
-    start.record(torch.cuda.current_stream(device))
+    for d, e in zip(devices, starts):
+        e.record(torch.cuda.current_stream(d))
     for _ in range(steps):
         step_fn()
         flush()
-    end.record(torch.cuda.current_stream(device))
-    torch.cuda.synchronize()
+    for d, e in zip(devices, ends):
+        torch.cuda.synchronize(d)
+        e.record(torch.cuda.current_stream(d))
+    sync_all()
+    wall = (time.perf_counter() - wall0) * 1e3
     if world > 1:
         dist.barrier()
-    wall = (time.perf_counter() - wall0) * 1e3
-    ms = start.elapsed_time(end)
+    ms = max([s.elapsed_time(e) for s, e in zip(starts, ends)] or [0.0])
     if world > 1:
-        t = torch.tensor([ms, wall], device=device, dtype=torch.float64)
+        t = torch.tensor([ms, wall], device=reduce_device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, wall = t.tolist()
     return ms, wall
 
 
+def metric_name(model):
+    """Constant across N (the experiment name pipeline-N lives in config)."""
+    return '%s GPipe training throughput' % MODEL_INFO[model]['metric']
+
+
+def free_port():
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        return s.getsockname()[1]
+
+
+def run_secondary(args, torch, dist, rank, local_rank, world, device):
+    """AmoebaNet-D(18,256) n{N}m32 of the same arm in a child process per rank.
+
+    Called after the headline measurement is finished and its memory released. The children form
+    their own process group on a fresh port; rank 0's child prints the JSON line this returns.
+    Any failure (exception, crash, timeout) becomes {'error': ...} - the headline is safe."""
+    n = args.gpus
+    if args.no_secondary or args.child or args.model != 'unet':
+        return None
+    if n not in EXPERIMENTS['amoebanetd']:
+        return {'skipped': 'the reference defines no %d-GPU AmoebaNet-D speed experiment '
+                           '(benchmarks/amoebanetd-speed/main.py: n2, n4, n8 only)' % n}
+    port = [free_port()]
+    if world > 1:
+        dist.broadcast_object_list(port, src=0)
+    env = dict(os.environ)
+    env.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port[0]), RANK=str(rank),
+               LOCAL_RANK=str(local_rank), WORLD_SIZE=str(world))
+    for key in ('TORCHELASTIC_RUN_ID', 'TORCHELASTIC_USE_AGENT_STORE', 'GROUP_RANK',
+                'ROLE_RANK', 'TORCHELASTIC_MAX_RESTARTS', 'TORCHELASTIC_RESTART_COUNT'):
+        env.pop(key, None)
+    cmd = [sys.executable, os.path.abspath(__file__), '--child', '--model', 'amoebanetd',
+           '--impl', args.impl, '--gpus', str(n), '--steps', str(min(args.steps, 5)),
+           '--warmup', str(max(3, min(args.warmup, 3)))]
+    if args.no_graphs:
+        cmd.append('--no-graphs')
+    if args.no_kernels:
+        cmd.append('--no-kernels')
+    try:
+        proc = subprocess.run(cmd, env=env, capture_output=True, text=True,
+                              timeout=args.secondary_timeout)
+        out, err, rc = proc.stdout, proc.stderr, proc.returncode
+    except subprocess.TimeoutExpired as exc:
+        out = exc.stdout.decode() if isinstance(exc.stdout, bytes) else (exc.stdout or '')
+        err, rc = 'timed out after %d s' % args.secondary_timeout, -1
+    if rank != 0:
+        return None
+    for line in reversed(out.splitlines()):
+        line = line.strip()
+        if line.startswith('{'):
+            try:
+                return json.loads(line)
+            except ValueError:
+                continue
+    return {'error': 'child exited %d: %s' % (rc, (err or '')[-600:])}
+
+
 # --------------------------------------------------------------------------- our arm
+def set_dropout(model, p=None, saved=None):
+    """p given: turn every (fused or plain) channel dropout off, returning what to restore;
+    saved given: restore."""
+    if saved is not None:
+        for m, value in saved:
+            m.p = value
+        return None
+    saved = []
+    for m in model.modules():
+        if hasattr(m, 'p') and isinstance(getattr(m, 'p'), float) and m.p != p:
+            saved.append((m, m.p))
+            m.p = p
+    return saved
+
+
+def check_numerics(torch, dist, F, args, make_pipe, model, plain, host_input, target, cfg,
+                   rank, world, device):
+    """One eager training step of the converted model and one of the plain PyTorch model (same
+    weights, dropout off, same pipeline layout) - every rank compares what it owns.
+
+    Returns {'loss_rel_diff', 'grad_norm_rel_diff', ...}; raises if they disagree beyond what
+    TF32 convolutions explain, so a run whose kernels are wrong on some rank never reports a
+    throughput."""
+    first, last = rank == 0, rank == world - 1
+    chunks, batch = cfg['chunks'], cfg['batch']
+    hw = MODEL_INFO[args.model]['hw']
+    total = float(batch * hw * hw) if args.model == 'unet' else float(batch)
+    # a slice of the mini-batch is enough: two micro-batches' worth per chunk count would change
+    # the micro-batch shapes, so keep the full shape but only one step
+    results = []
+    for tag, net in (('plain', plain), ('sm100', model)):
+        saved = set_dropout(net, 0.0)
+        pipe = make_pipe(net, graphs=False, name='check-' + tag)
+        stage = pipe.model()
+        stage.train()
+        dev_in = host_input.to(device) if first else None
+        outs = pipe.forward(dev_in)
+        if last:
+            losses = [loss_sum(F, args.model, o, t) / total
+                      for o, t in zip(outs, target.chunk(chunks))]
+            pipe.backward(losses)
+            loss = float(torch.stack([x.detach() for x in losses]).sum().item())
+        else:
+            pipe.backward(None)
+            loss = 0.0
+        sq = torch.zeros((), device=device, dtype=torch.float64)
+        for prm in stage.parameters():
+            if prm.grad is not None:
+                sq += prm.grad.double().pow(2).sum()
+                prm.grad = None
+        results.append((loss, float(sq.sqrt().item())))
+        set_dropout(net, saved=saved)
+        del pipe, outs
+    (loss_a, g_a), (loss_b, g_b) = results
+    mine = [abs(loss_a - loss_b) / max(abs(loss_a), 1e-12) if last else 0.0,
+            abs(g_a - g_b) / max(g_a, 1e-12)]
+    if world > 1:
+        t = torch.tensor(mine, device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        mine = t.tolist()
+        lt = torch.tensor([loss_a, loss_b], device=device, dtype=torch.float64)
+        dist.all_reduce(lt)                 # only the last rank contributes non-zeros
+        loss_a, loss_b = lt.tolist()
+    report = {'loss_plain_torch': loss_a, 'loss_sm100': loss_b, 'loss_rel_diff': mine[0],
+              'grad_norm_rel_diff_max_over_ranks': mine[1],
+              'tolerance': {'loss': 1e-2, 'grad_norm': 5e-2},
+              'how': 'one eager step each, same weights and input, dropout off, before timing'}
+    if not (mine[0] < 1e-2 and mine[1] < 5e-2):
+        raise AssertionError('numerics check failed: %s' % json.dumps(report))
+    return report
+
+
 def run_ours(args):
+    import gc
     import torch
     import torch.distributed as dist
     import torch.nn.functional as F
@@ -231,7 +386,10 @@ def run_ours(args):
 
     torch.manual_seed(0)
     model = build_model(dict(unet=unet, amoebanetd=amoebanetd, resnet101=resnet101), args.model)
+    plain = None
     if not args.no_kernels:
+        if not args.no_check:
+            plain = copy.deepcopy(model)
         model = ops.convert_to_sm100(model)
 
     batch, chunks, balance = cfg['batch'], cfg['chunks'], cfg['balance']
@@ -242,6 +400,8 @@ def run_ours(args):
     # One rank per stage, every stage pass replayed from CUDA graphs - also for a single stage
     # (N=1), where the eager single-process GPipe is host-bound (about 2300 launches per step).
     stage_mode = world > 1 or (n == 1 and not args.no_graphs)
+    numerics = None
+    target = None
     if not stage_mode:
         pipe = GPipe(model, balance, devices=[device] * 1 if n == 1 else
                      [torch.device('cuda', k) for k in range(n)],
@@ -260,18 +420,30 @@ def run_ours(args):
             return loss
     else:
         from torchgpipe_b200.distributed import DistributedGPipe, ProcessGroupTransport, context
-        workers = {r: f'stage{r}' for r in range(world)}
-        if world > 1:
-            tp = ProcessGroupTransport(device)
-        else:
-            tp = None                                   # in-process channels; nothing is sent
-            context.worker(workers[0], chunks).__enter__()
-        pipe = DistributedGPipe(model, rank, workers, balance, chunks, device=device,
-                                checkpoint='except_last', transport=tp,
-                                cuda_graphs=not args.no_graphs)
+        entered = []
+
+        def make_pipe(net, graphs, name='stage'):
+            workers = {r: f'{name}{r}' for r in range(world)}
+            if world > 1:
+                tp = ProcessGroupTransport(device)
+            else:
+                tp = None                               # in-process channels; nothing is sent
+                ctx = context.worker(workers[0], chunks)
+                ctx.__enter__()
+                entered.append(ctx)
+            return DistributedGPipe(net, rank, workers, balance, chunks, device=device,
+                                    checkpoint='except_last', transport=tp, cuda_graphs=graphs)
+
+        target = make_target(torch, args.model, batch, hw, device) if last else None
+        if plain is not None:
+            numerics = check_numerics(torch, dist, F, args, make_pipe, model, plain, host_input,
+                                      target, cfg, rank, world, device)
+            del plain
+            gc.collect()
+            torch.cuda.empty_cache()
+        pipe = make_pipe(model, graphs=not args.no_graphs)
         params = list(pipe.model().parameters())
         dev_input = host_input.to(device) if first else None
-        target = make_target(torch, args.model, batch, hw, device) if last else None
         # normaliser of the mini-batch mean loss: elements for BCE, samples for cross-entropy
         total = float(batch * hw * hw) if args.model == 'unet' else float(batch)
 
@@ -291,25 +463,25 @@ def run_ours(args):
 
     opt = SGD(params, lr=0.1)
     flush = L2Flusher(torch, device)
+    my_devices = [device] if stage_mode else list(dict.fromkeys(pipe.devices))
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
     ops.reset_launch_count()
 
     # device-timed, inputs resident on the device
-    if sampler:
-        sampler.start()
-    launches_before = ops.launch_count()
-    # warm-up happens inside timed_loop; count launches over the timed part only
     for _ in range(args.warmup):
         step()
         flush()
+
     def total_launches():
         replayed = pipe.native_launches_replayed() if hasattr(pipe, 'native_launches_replayed') \
             else 0
         return ops.launch_count() + replayed
 
+    if sampler:
+        sampler.start()
     launches_before = total_launches()
-    ms, _ = timed_loop(torch, dist, lambda: step(), args.steps, 0, device, flush, world)
+    ms, _ = timed_loop(torch, dist, lambda: step(), args.steps, 0, my_devices, flush, world, device)
     launches = total_launches() - launches_before
     clocks = sampler.stop() if sampler else None
 
@@ -323,7 +495,8 @@ def run_ours(args):
         if loss is not None:
             loss_host.copy_(loss.detach().reshape(1), non_blocking=False)
 
-    _, e2e_wall = timed_loop(torch, dist, e2e_step, args.steps, 1, device, flush, world)
+    _, e2e_wall = timed_loop(torch, dist, e2e_step, args.steps, 1, my_devices, flush, world,
+                             device)
 
     pipeline_report = None
     if world > 1:
@@ -337,25 +510,33 @@ def run_ours(args):
         pipe.timeline = False
         gathered = [None] * world
         dist.all_gather_object(gathered, mine)
-        pipeline_report = {'per_rank': [{k: round(v, 3) for k, v in (g or {}).items()}
+        pipeline_report = {'ideal_bubble_frac': (n - 1) / (chunks + n - 1),
+                           'per_rank': [{k: round(v, 3) for k, v in (g or {}).items()}
                                         for g in gathered]}
 
     samples = batch * args.steps
     value = samples / (ms / 1e3)
     e2e_value = samples / (e2e_wall / 1e3)
     result = {
-        'metric': '%s training throughput, GPipe pipeline-%d' % (MODEL_INFO[args.model]['metric'], n),
+        'metric': metric_name(args.model),
         'impl': 'ours',
         'value': value, 'unit': 'samples/s', 'n_gpus': n, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True,
-        'scaling': 'weak', 'vs_baseline': value / PUBLISHED[args.model][n],
+        'scaling': 'weak',
+        # the only published numbers are the reference authors' Tesla P40
+        # runs; the same-box reference arm (--impl reference) is the comparison that matters
+        'vs_baseline': value / PUBLISHED[args.model][n],
+        'baseline_hardware': 'Tesla P40 (published); same-box B200 ratio: run --impl reference',
         'dtype': 'fp32 storage / tf32 tensor-core conv', 'data': 'synthetic',
         'config': {'model': MODEL_INFO[args.model]['name'],
+                   'experiment': 'pipeline-%d' % n,
                    'global_batch': batch, 'chunks': chunks, 'balance': balance,
                    'input': [3, MODEL_INFO[args.model]['hw'], MODEL_INFO[args.model]['hw']],
                    'checkpoint': 'except_last',
                    'optimizer': 'SGD(lr=0.1)', 'loss': MODEL_INFO[args.model]['loss'],
                    'parallelism': 'pp%d' % n,
+                   'scaling_note': 'batch and micro-batch count per N are the reference\'s own '
+                                   'experiment definitions (80/512/512/640 for U-Net)',
                    'transport': 'single-process' if world == 1 else 'nccl-p2p',
                    'engine': 'DistributedGPipe (one rank per stage)' if stage_mode
                    else 'GPipe (single process)',
@@ -367,8 +548,16 @@ def run_ours(args):
                 'h2d_bytes_per_step': host_input.numel() * 4, 'd2h_bytes_per_step': 4,
                 'ms_per_step': e2e_wall / args.steps},
         'gpu_launches': launches,
+        'numerics': numerics,
         'pipeline': pipeline_report,
     }
+    # release everything before the secondary model runs in its own processes
+    del pipe, opt, params, step, e2e_step, model, flush, dev_input, stage_in, target
+    gc.collect()
+    torch.cuda.empty_cache()
+    secondary = run_secondary(args, torch, dist, rank, local_rank, world, device)
+    if secondary is not None:
+        result['secondary'] = secondary
     if rank == 0:
         print(json.dumps(result), flush=True)
     if world > 1:
@@ -377,20 +566,46 @@ def run_ours(args):
 
 
 # --------------------------------------------------------------------------- reference arm
+def ensure_reference(here):
+    """baseline/_ref is staged by __graft_entry__.build() on the build box and travels with the
+    working tree; if it is missing, try the same staging script here (works wherever
+    /root/reference and /opt/wheelhouse exist). Returns (ref_root or None, reason)."""
+    ref_root = os.path.join(here, 'baseline', '_ref')
+    marker = os.path.join(ref_root, 'torchgpipe', '__init__.py')
+    if os.path.exists(marker):
+        return ref_root, ''
+    if not os.path.isdir('/root/reference'):
+        return None, ('baseline/_ref is missing and /root/reference is not on this machine '
+                      '(python -c "import __graft_entry__ as g; g.build()" stages it)')
+    rank, _, world = dist_env()
+    if rank == 0:
+        proc = subprocess.run(['bash', os.path.join(here, 'baseline', 'stage_reference.sh')],
+                              capture_output=True, text=True)
+        why = (proc.stdout + proc.stderr)[-300:].replace('\n', ' ')
+    else:
+        why = ''
+        for _ in range(600):                # rank 0 is staging
+            if os.path.exists(marker):
+                break
+            time.sleep(0.5)
+    if os.path.exists(marker):
+        return ref_root, ''
+    return None, 'baseline/stage_reference.sh failed: ' + why
+
+
 def run_reference(args):
     rank, local_rank, world = dist_env()
     here = os.path.dirname(os.path.abspath(__file__))
-    ref_root = os.path.join(here, 'baseline', '_ref')
-    if not os.path.isdir(os.path.join(ref_root, 'torchgpipe')):
+    ref_root, why = ensure_reference(here)
+    if ref_root is None:
         if rank == 0:
-            print(json.dumps({'impl': 'reference',
-                              'unavailable': 'baseline/_ref is missing (run '
-                                             'baseline/stage_reference.sh)'}), flush=True)
+            print(json.dumps({'impl': 'reference', 'unavailable': why}), flush=True)
         return
     # Reference first on the path; this repo's package is never imported on this arm.
     sys.path.insert(0, os.path.join(ref_root, 'benchmarks_models'))
     sys.path.insert(0, ref_root)
 
+    import gc
     import torch
     import torch.distributed as dist
     import torch.nn.functional as F
@@ -416,6 +631,7 @@ def run_reference(args):
     host_input = torch.rand(batch, 3, hw, hw).pin_memory()
     loss_host = torch.zeros(1).pin_memory()
 
+    devices = []
     if driver:
         torch.manual_seed(0)
         model = build_model(dict(unet=unet, amoebanetd=amoebanetd, resnet101=resnet101),
@@ -434,57 +650,17 @@ def run_reference(args):
             opt.step()
             opt.zero_grad()
             return loss
-
-        def sync_all():
-            for d in devices:
-                torch.cuda.synchronize(d)
     else:
         def step(inp=None):
             return None
 
-        def sync_all():
-            torch.cuda.synchronize()
-
-    def timed(step_fn, steps, warmup):
-        for _ in range(warmup):
-            step_fn()
-            flush()
-        sync_all()
-        if world > 1:
-            dist.barrier()
-        sync_all()
-        ms = 0.0
-        wall0 = time.perf_counter()
-        if driver:
-            # one event pair per pipeline device; the step is done when the slowest is done
-            starts = [torch.cuda.Event(enable_timing=True) for _ in devices]
-            ends = [torch.cuda.Event(enable_timing=True) for _ in devices]
-            for d, e in zip(devices, starts):
-                e.record(torch.cuda.current_stream(d))
-        for _ in range(steps):
-            step_fn()
-            flush()
-        if driver:
-            for d, e in zip(devices, ends):
-                e.record(torch.cuda.current_stream(d))
-        sync_all()
-        if world > 1:
-            dist.barrier()
-        wall = (time.perf_counter() - wall0) * 1e3
-        if driver:
-            ms = max(s.elapsed_time(e) for s, e in zip(starts, ends))
-            # stages start at different times: the device-side span cannot be shorter than
-            # the longest single-device span; wall bounds it from above.
-        if world > 1:
-            t = torch.tensor([ms, wall], device=device, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms, wall = t.tolist()
-        return ms, wall
-
     sampler = ClockSampler(local_rank) if rank == 0 else None
+    for _ in range(args.warmup):
+        step()
+        flush()
     if sampler:
         sampler.start()
-    ms, _ = timed(lambda: step(), args.steps, args.warmup)
+    ms, _ = timed_loop(torch, dist, lambda: step(), args.steps, 0, devices, flush, world, device)
     clocks = sampler.stop() if sampler else None
 
     def e2e_step():
@@ -493,18 +669,20 @@ def run_reference(args):
             loss = step(stage_in)
             loss_host.copy_(loss.detach().reshape(1).to('cpu'))
 
-    _, e2e_wall = timed(e2e_step, args.steps, 1)
+    _, e2e_wall = timed_loop(torch, dist, e2e_step, args.steps, 1, devices, flush, world, device)
 
     samples = batch * args.steps
     value = samples / (ms / 1e3)
     result = {
-        'metric': '%s training throughput, GPipe pipeline-%d' % (MODEL_INFO[args.model]['metric'], n),
+        'metric': metric_name(args.model),
         'impl': 'reference',
         'value': value, 'unit': 'samples/s', 'n_gpus': n, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': value / PUBLISHED[args.model][n],
+        'baseline_hardware': 'Tesla P40 (published)',
         'dtype': 'fp32 storage / tf32 cuDNN conv (PyTorch defaults)', 'data': 'synthetic',
         'config': {'model': MODEL_INFO[args.model]['name'],
+                   'experiment': 'pipeline-%d' % n,
                    'global_batch': batch, 'chunks': chunks, 'balance': balance,
                    'input': [3, MODEL_INFO[args.model]['hw'], MODEL_INFO[args.model]['hw']],
                    'checkpoint': 'except_last',
@@ -518,6 +696,14 @@ def run_reference(args):
                 'ms_per_step': e2e_wall / args.steps},
         'gpu_launches': 0,
     }
+    if driver:
+        del pipe, opt, model, dev_input, stage_in, target, step, e2e_step
+    del flush
+    gc.collect()
+    torch.cuda.empty_cache()
+    secondary = run_secondary(args, torch, dist, rank, local_rank, world, device)
+    if secondary is not None:
+        result['secondary'] = secondary
     if rank == 0:
         print(json.dumps(result), flush=True)
     if world > 1:
@@ -537,6 +723,12 @@ def main():
                    help='ours arm, N>1: issue stage kernels eagerly instead of replaying CUDA graphs')
     p.add_argument('--no-kernels', action='store_true',
                    help='ours arm: keep torch/cuDNN ops (diagnostic; not the product path)')
+    p.add_argument('--no-check', action='store_true',
+                   help='ours arm: skip the plain-PyTorch numerics comparison before timing')
+    p.add_argument('--no-secondary', action='store_true',
+                   help='do not measure AmoebaNet-D(18,256) n{N}m32 after the U-Net headline')
+    p.add_argument('--secondary-timeout', type=int, default=900)
+    p.add_argument('--child', action='store_true', help=argparse.SUPPRESS)
     args = p.parse_args()
     if args.gpus not in EXPERIMENTS[args.model]:
         raise SystemExit('--gpus must be one of %s' % sorted(EXPERIMENTS[args.model]))

@@ -550,6 +550,20 @@ extern "C" int tgb_conv2d_wgrad_tf32_noalloc(const float* dy, const float* x, fl
     return set_error("wgrad_noalloc: this problem needs %lld bytes of scratch but the built-in "
                      "buffer holds %lld; call tgb_conv2d_wgrad_tf32 with your own scratch instead",
                      need, kNoAllocScratchBytes);
+  // The built-in buffer of the CURRENT device is used and the launch goes to the current device:
+  // tensors that live on another GPU mean the caller forgot cudaSetDevice. Refuse that instead
+  // of handing the kernels an address that belongs to a different GPU.
+  {
+    int dev = -1;
+    cudaPointerAttributes attr;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaPointerGetAttributes(&attr, dw) == cudaSuccess &&
+        attr.type == cudaMemoryTypeDevice && attr.device != dev)
+      return set_error("wgrad_noalloc: dw lives on device %d but device %d is current; make the "
+                       "device that owns the tensors (and the stream) current before the call",
+                       attr.device, dev);
+    cudaGetLastError();       // a failed attribute query must not stick
+  }
   float* scratch = nullptr;
   if (noalloc_scratch_ptr(&scratch)) return 1;
   // Every partial the reduction reads is written by the kernel of this same call first, so

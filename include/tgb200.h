@@ -68,7 +68,11 @@ int tgb_conv2d_wgrad_tf32(const float* dy, const float* x, float* dw, float* scr
  *   - The one buffer is shared by all calls on a device and keeps whatever the previous call
  *     wrote; each call overwrites every partial before reading it, so nothing needs clearing.
  *     Two calls that can run on the GPU at the same time (different streams, no ordering
- *     between them) race on the buffer: serialise them. */
+ *     between them) race on the buffer: serialise them.
+ *   - Each GPU has its own copy of the buffer and the call uses the copy of the CURRENT device:
+ *     the device that owns dy / x / dw and `stream` must be current (cudaSetDevice) when calling,
+ *     as for every entry point here. A dw that lives on a different GPU than the current one is
+ *     refused with an error. */
 #define TGB_WGRAD_NOALLOC_SCRATCH_BYTES (32ll << 20)
 int tgb_conv2d_wgrad_tf32_noalloc(const float* dy, const float* x, float* dw,
                                   int N, int H, int W, int C, int K, int R, int S,

@@ -369,3 +369,61 @@ def test_static_shape_transport_refuses_a_changed_shape_and_dynamic_one_follows_
     mp.spawn(_shape_worker, args=(2, port, ret), nprocs=2, join=True)
     assert ret['error'] is not None and 'static_shapes' in ret['error']
     assert ret['got'] == (6.0, 12.0, (2, 3), ((5,), (1, 2)))
+
+
+def _silent_peer_worker(rank, world, port, ret):
+    import time
+    import torch.distributed as dist
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from torchgpipe_b200.distributed.transport import ProcessGroupTransport
+        tp = ProcessGroupTransport(torch.device('cpu'), timeout=1.5)
+        if rank == 1:
+            t0 = time.monotonic()
+            try:
+                # `like` given: no header round-trip, the payload itself never comes
+                tp.recv(0, ('bwd', 0, 0), like=torch.zeros(3))
+                ret['error'] = None
+            except TimeoutError as exc:
+                ret['error'] = str(exc)
+            ret['waited'] = time.monotonic() - t0
+        else:
+            time.sleep(4.0)         # the peer is alive but never sends
+    finally:
+        try:
+            dist.destroy_process_group()
+        except Exception:
+            pass
+
+
+@pytest.mark.timeout(120)
+def test_receive_from_a_silent_peer_times_out_instead_of_hanging():
+    # the reference's Queue.get / rpc wait has no deadline (distributed/context.py:141)
+    port = 35500 + os.getpid() % 2000
+    manager = mp.Manager()
+    ret = manager.dict()
+    mp.spawn(_silent_peer_worker, args=(2, port, ret), nprocs=2, join=True)
+    assert ret['error'] is not None and 'did not arrive' in ret['error']
+    assert 1.0 < ret['waited'] < 30.0
+
+
+def test_channel_get_times_out_with_a_message_naming_the_waiter():
+    import queue
+    with context.worker('lonely', 1):
+        with pytest.raises(context.ChannelTimeout, match="worker 'lonely'"):
+            context.get_forward('lonely', 0, timeout=0.05)
+        with pytest.raises(queue.Empty):            # the documented older catch still works
+            context.get_backward('lonely', 0, timeout=0.05)
+        with pytest.raises(TimeoutError):
+            context.get_target('lonely', timeout=0.05)
+
+
+def test_default_channel_timeout_comes_from_the_environment(monkeypatch):
+    monkeypatch.setenv('TGB_CHANNEL_TIMEOUT', '12.5')
+    assert context.default_timeout() == 12.5
+    monkeypatch.setenv('TGB_CHANNEL_TIMEOUT', '0')
+    assert context.default_timeout() is None        # wait forever, like the reference
+    monkeypatch.delenv('TGB_CHANNEL_TIMEOUT')
+    assert context.default_timeout() == 1800.0

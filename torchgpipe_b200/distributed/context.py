@@ -8,21 +8,50 @@ backend (tests, debugging, or an RPC layer calling ``put_*`` remotely); the
 GPU path uses :class:`~torchgpipe_b200.distributed.transport.ProcessGroupTransport`.
 
 API contract: reference ``torchgpipe/distributed/context.py:19-193``. One
-addition: ``get_*`` take an optional ``timeout`` (seconds) so a dead peer
-raises ``queue.Empty`` instead of blocking forever.
+addition: ``get_*`` give up after ``timeout`` seconds (default
+:func:`default_timeout`: ``TGB_CHANNEL_TIMEOUT``, else 1800 s; ``0`` or ``inf``
+= wait forever like the reference, ``context.py:141``) and raise
+:class:`ChannelTimeout`, so a dead peer ends the job instead of hanging it.
 """
+import math
+import os
 from contextlib import contextmanager
 from functools import wraps
-from queue import Queue
+from queue import Empty, Queue
 from typing import Any, Callable, Dict, Generator, List, Optional, Tuple, Union
 
 from torch import Tensor
 
 __all__ = ['TrainingContext', 'GlobalContext', 'worker', 'distributed', 'put_forward',
-           'get_forward', 'put_backward', 'get_backward', 'put_target', 'get_target']
+           'get_forward', 'put_backward', 'get_backward', 'put_target', 'get_target',
+           'ChannelTimeout', 'default_timeout']
 
 Tensors = Tuple[Tensor, ...]
 TensorOrTensors = Union[Tensor, Tensors]
+
+
+class ChannelTimeout(TimeoutError, Empty):
+    """Nothing arrived on a channel in time (also catchable as ``queue.Empty``)."""
+
+
+def default_timeout() -> Optional[float]:
+    """Seconds a ``get_*`` waits when no ``timeout`` is given; ``None`` = forever."""
+    raw = os.environ.get('TGB_CHANNEL_TIMEOUT', '1800')
+    try:
+        value = float(raw)
+    except ValueError:
+        return 1800.0
+    return None if value <= 0 or math.isinf(value) else value
+
+
+def _take(queue: Queue, timeout: Optional[float], what: str) -> Any:
+    if timeout is None:
+        timeout = default_timeout()
+    try:
+        return queue.get(timeout=timeout)
+    except Empty:
+        raise ChannelTimeout(f'no {what} within {timeout:g} s: the peer stage died or never '
+                             'sent it (TGB_CHANNEL_TIMEOUT changes the limit)') from None
 
 
 class TrainingContext:
@@ -81,7 +110,8 @@ def put_forward(context_name: str, id: int, value: TensorOrTensors) -> None:
 
 def get_forward(name: str, id: int, timeout: Optional[float] = None) -> TensorOrTensors:
     """Blocks until the input of micro-batch ``id`` has been delivered to ``name``."""
-    return GlobalContext.get_context(name).forward_channels[id].get(timeout=timeout)
+    return _take(GlobalContext.get_context(name).forward_channels[id], timeout,
+                 f'input of micro-batch {id} for worker {name!r}')
 
 
 def put_backward(name: str, id: int, value: TensorOrTensors) -> None:
@@ -90,7 +120,8 @@ def put_backward(name: str, id: int, value: TensorOrTensors) -> None:
 
 
 def get_backward(name: str, id: int, timeout: Optional[float] = None) -> TensorOrTensors:
-    return GlobalContext.get_context(name).backward_channels[id].get(timeout=timeout)
+    return _take(GlobalContext.get_context(name).backward_channels[id], timeout,
+                 f'gradient of micro-batch {id} for worker {name!r}')
 
 
 def put_target(name: str, value: TensorOrTensors) -> None:
@@ -99,4 +130,5 @@ def put_target(name: str, value: TensorOrTensors) -> None:
 
 
 def get_target(name: str, timeout: Optional[float] = None) -> TensorOrTensors:
-    return GlobalContext.get_context(name).target_channel.get(timeout=timeout)
+    return _take(GlobalContext.get_context(name).target_channel, timeout,
+                 f'target for worker {name!r}')

@@ -228,11 +228,32 @@ class DistributedGPipe:
         self._live = 0      # micro-batches produced by the latest forward()
         self.cuda_graphs = bool(cuda_graphs) and device is not None and \
             torch.device(device).type == 'cuda'
+        if self.cuda_graphs:
+            self._refuse_host_state_under_graphs(partition, deferred_batch_norm)
         self._graphed: Dict[Tuple[int, bool], Any] = {}
         #: set to True to record CUDA events around every stage pass (see timeline_report)
         self.timeline = False
         self._marks: List[Tuple[str, Any, Any, Any]] = []
         self._bytes_received = 0
+
+    @staticmethod
+    def _refuse_host_state_under_graphs(partition: nn.Module, deferred_batch_norm: bool) -> None:
+        """A replayed graph runs kernels only: Python-side counters and branches are frozen at
+        capture time. Refuse the layer configurations whose correctness depends on them."""
+        from torch.nn.modules.batchnorm import _BatchNorm
+        if deferred_batch_norm or any(isinstance(m, DeferredBatchNorm) or
+                                      getattr(m, 'deferred_chunks', 0) > 0
+                                      for m in partition.modules()):
+            raise ValueError(
+                'cuda_graphs=True cannot be combined with deferred_batch_norm=True: the '
+                'micro-batch counter and the commit of the accumulated statistics are host-side '
+                'state that a graph replay does not execute')
+        for m in partition.modules():
+            tracks = getattr(m, 'track_running_stats', False)
+            if isinstance(m, _BatchNorm) and tracks and getattr(m, 'momentum', 0.1) is None:
+                raise ValueError(
+                    'cuda_graphs=True needs BatchNorm layers with a numeric momentum: '
+                    'momentum=None (cumulative average) reads num_batches_tracked on the host')
 
     # -- topology ----------------------------------------------------------------
     @property
@@ -572,12 +593,23 @@ class DistributedGPipe:
         leaves = flight.leaves
         nb = flight.n_boundary
         if not self.is_first:
-            grads = tuple(torch.zeros_like(x) if g is None else g
-                          for x, g in zip(leaves[:nb], gin[:nb]))
+            grads = tuple(self._like_leaf(x, g) for x, g in zip(leaves[:nb], gin[:nb]))
             tp.send(self.rank - 1, ('bwd', mb, 0), grads[0] if flight.atomic_in else grads)
         for (slot, src, _), x, g in zip(self._routes_in, leaves[nb:], gin[nb:]):
             if x.is_floating_point():
-                tp.send(src, ('skip_grad', mb, slot), torch.zeros_like(x) if g is None else g)
+                tp.send(src, ('skip_grad', mb, slot), self._like_leaf(x, g))
+
+    @staticmethod
+    def _like_leaf(leaf: Tensor, grad: Optional[Tensor]) -> Tensor:
+        """The gradient to ship for ``leaf``: the peer's receive buffer has the (dense) layout of
+        the tensor it sent forward and the transport moves raw bytes, so match that layout."""
+        if grad is None:
+            return torch.zeros_like(leaf)
+        if grad.stride() != leaf.stride():
+            fmt = torch.channels_last if (leaf.dim() == 4 and not leaf.is_contiguous()) \
+                else torch.contiguous_format
+            grad = grad.contiguous(memory_format=fmt)
+        return grad
 
     @staticmethod
     def _grad_of(leaf: Tensor) -> Tensor:

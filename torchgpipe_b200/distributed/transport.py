@@ -18,7 +18,21 @@ and ``'target'``.
   (static shapes per micro-batch index), so steady-state traffic is payload
   only. For a pair of ranks, both ends issue their operations in the same
   program order, which is what NCCL point-to-point requires.
+
+Failure detection (the reference's ``Queue.get`` waits forever,
+``torchgpipe/distributed/context.py:141``): every receive has a deadline.
+On CPU (gloo) the wait itself times out and raises ``TimeoutError``. On GPUs a
+receive only *orders* the compute stream behind the transfer, so the host
+cannot time out inside it; a watchdog thread follows a CUDA event recorded
+after each receive and, when one stays pending past the deadline, reports
+which message is missing, aborts the process group and ends the process so the
+launcher tears the job down instead of leaving every rank spinning.
 """
+import datetime
+import os
+import sys
+import threading
+import time
 from collections import defaultdict
 from queue import Queue
 from typing import Any, Dict, List, Optional, Sequence, Tuple, Union
@@ -92,7 +106,9 @@ class ChannelTransport(Transport):
             return self.owner._get(name, mb, False)
         if kind == 'bwd':
             return self.owner._get(name, mb, True)
-        return ChannelTransport._extra[(name, key)].get(timeout=self.timeout)
+        from torchgpipe_b200.distributed.context import _take
+        return _take(ChannelTransport._extra[(name, key)], self.timeout,
+                     f'{kind} message of micro-batch {mb} for worker {name!r}')
 
 
 class ProcessGroupTransport(Transport):
@@ -100,7 +116,7 @@ class ProcessGroupTransport(Transport):
 
     def __init__(self, device: Optional[torch.device] = None, group: Any = None,
                  ranks: Optional[Dict[int, int]] = None, static_shapes: bool = True,
-                 pair_groups: bool = False) -> None:
+                 pair_groups: bool = False, timeout: Optional[float] = None) -> None:
         import torch.distributed as dist
         if not dist.is_initialized():
             raise RuntimeError('torch.distributed must be initialised before creating a '
@@ -115,6 +131,49 @@ class ProcessGroupTransport(Transport):
         self._known_send: Dict[Tuple[int, Key], Any] = {}
         self._known_recv: Dict[Tuple[int, Key], Any] = {}
         self._pending: List[Any] = []
+        if timeout is None:
+            timeout = float(os.environ.get('TGB_P2P_TIMEOUT', '1800'))
+        #: seconds a receive may stay incomplete (<= 0: no deadline)
+        self.timeout = timeout if timeout > 0 else None
+        self._watch: List[Tuple[Any, float, str]] = []
+        self._watch_lock = threading.Lock()
+        self._watchdog: Optional[threading.Thread] = None
+
+    # -- failure detection -----------------------------------------------------
+    def _watch_receive(self, what: str) -> None:
+        """GPU path: follow the receive that was just ordered into the current stream."""
+        if self.timeout is None or self.device.type != 'cuda':
+            return
+        event = torch.cuda.Event()
+        event.record(torch.cuda.current_stream(self.device))
+        with self._watch_lock:
+            self._watch.append((event, time.monotonic() + self.timeout, what))
+            if self._watchdog is None:
+                self._watchdog = threading.Thread(target=self._watchdog_loop, daemon=True,
+                                                  name='tgb-p2p-watchdog')
+                self._watchdog.start()
+
+    def _watchdog_loop(self) -> None:
+        period = min(1.0, max(0.05, (self.timeout or 1.0) / 20))
+        while True:
+            time.sleep(period)
+            now = time.monotonic()
+            with self._watch_lock:
+                self._watch = [w for w in self._watch if not w[0].query()]
+                expired = [w for w in self._watch if w[1] < now]
+            if expired:
+                self._abort(expired[0][2])
+
+    def _abort(self, what: str) -> None:
+        print(f'[torchgpipe_b200] rank {self.dist.get_rank()}: {what} did not arrive within '
+              f'{self.timeout:g} s - a peer stage died or stalled; aborting the process group',
+              file=sys.stderr, flush=True)
+        try:
+            from torch.distributed.distributed_c10d import _abort_process_group
+            _abort_process_group(self.group)
+        except Exception:       # older releases: nothing to abort with
+            pass
+        os._exit(70)
 
     def _global(self, stage_rank: int) -> int:
         return stage_rank if self.ranks is None else self.ranks[stage_rank]
@@ -200,7 +259,9 @@ class ProcessGroupTransport(Transport):
         tensors = (value,) if atomic else tuple(value)
         if key[0] not in ('bwd', 'skip_grad'):
             # Gradient messages never need a header: the receiver passes `like`.
-            meta = (atomic, tuple((t.dtype, tuple(t.shape)) for t in tensors))
+            meta = (atomic, tuple((t.dtype, tuple(t.shape), t.dim() == 4 and not t.is_contiguous()
+                                   and t.is_contiguous(memory_format=torch.channels_last))
+                                  for t in tensors))
             known = self._known_send.get(slot)
             if not self.static_shapes or known is None:
                 self._pending.append(
@@ -209,8 +270,9 @@ class ProcessGroupTransport(Transport):
             elif known != meta:
                 # the receiver allocates from the header it cached on the first message
                 raise ValueError(
-                    f'message {key} to stage {dst} changed shape or dtype ({known[1]} -> '
-                    f'{meta[1]}) but this transport was created with static_shapes=True; use '
+                    f'message {key} to stage {dst} changed shape, dtype or memory format '
+                    f'({known[1]} -> {meta[1]}) but this transport was created with '
+                    'static_shapes=True; use '
                     'ProcessGroupTransport(static_shapes=False) for varying batch sizes')
         # Completed sends are dropped right away: a pending handle keeps its tensor alive, and
         # activations are large (a leaked handle per message grows memory by GBs per step).
@@ -235,7 +297,9 @@ class ProcessGroupTransport(Transport):
             atomic, meta = self._known_recv[slot]
         else:
             header = torch.empty(_HEADER_LEN, dtype=torch.int64, device=self.device)
-            self.dist.recv(header, peer, group=group)
+            self._wait(self.dist.irecv(header, peer, group=group),
+                       f'header of message {key} from stage {src}')
+            self._watch_receive(f'header of message {key} from stage {src}')
             atomic, meta = self._decode(header)
             self._known_recv[slot] = (atomic, meta)
         out = []
@@ -246,9 +310,25 @@ class ProcessGroupTransport(Transport):
                               else torch.contiguous_format)
             works.append(self.dist.irecv(buf, peer, group=group))
             out.append(buf)
+        what = f'message {key} from stage {src}'
         for w in works:
-            w.wait()        # NCCL: orders the current stream behind the transfer
+            self._wait(w, what)
+        self._watch_receive(what)
         return out[0] if atomic else tuple(out)
+
+    def _wait(self, work: Any, what: str) -> None:
+        if self.device.type == 'cuda' or self.timeout is None:
+            work.wait()     # NCCL: orders the current stream behind the transfer
+            return
+        try:
+            done = work.wait(datetime.timedelta(seconds=self.timeout))
+        except RuntimeError as exc:     # gloo reports an expired wait as RuntimeError
+            if 'time' in str(exc).lower():
+                raise TimeoutError(f'{what} did not arrive within {self.timeout:g} s: the peer '
+                                   'stage died or never sent it') from None
+            raise
+        if done is False:
+            raise TimeoutError(f'{what} did not arrive within {self.timeout:g} s')
 
     def _reap(self) -> None:
         self._pending = [w for w in self._pending if not w.is_completed()]

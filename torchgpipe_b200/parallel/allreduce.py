@@ -12,6 +12,7 @@ NCCL ``all_reduce`` on the same bucket is the baseline these numbers are compare
 set up (single rank, CPU, or a platform without peer access).
 """
 import ctypes
+import os
 from typing import Any, Optional
 
 import torch
@@ -76,6 +77,19 @@ class SymmetricBuffer:
     def has_multicast(self) -> bool:
         return self.multicast_ptr != 0
 
+    def check(self) -> None:
+        """Raises if a fused all-reduce on this buffer gave up waiting for a peer.
+
+        The kernel returns early (leaving the buffer partially reduced) when a peer misses a
+        barrier for longer than ``timeout_ms`` and records that in ``error_flag``. Reading the
+        flag synchronises with the stream the all-reduce ran on, so call it once per step,
+        before ``optimizer.step()``. The flag is cleared when the error is raised."""
+        if int(self.error_flag.item()) != 0:
+            self.error_flag.zero_()
+            raise RuntimeError(
+                f'fused all-reduce timed out on rank {self.rank} of {self.world}: a peer did '
+                'not reach the barrier; the gradients in this buffer are not fully reduced')
+
 
 def fused_allreduce_(buf: SymmetricBuffer, scale: float = 1.0, cast_out: Optional[Tensor] = None,
                      multicast: Optional[bool] = None, timeout_ms: int = 20000,
@@ -84,12 +98,15 @@ def fused_allreduce_(buf: SymmetricBuffer, scale: float = 1.0, cast_out: Optiona
 
     Enqueued on the current stream; every rank of ``buf.group`` must call it (same order).
     ``cast_out``: optional local bf16 tensor of ``buf.numel`` elements receiving a copy.
-    ``multicast``: ``True``/``False`` forces the NVLS / P2P variant; default picks NVLS when the
-    fabric supports it and there are more than two replicas.
+    ``multicast``: ``True`` selects the NVLS variant (``multimem.ld_reduce`` / ``multimem.st``
+    through the switch), ``False`` the peer-load variant. The default is the peer-load variant;
+    ``TGB_ALLREDUCE_NVLS=1`` makes NVLS the default where the buffer has a multicast mapping.
+    Call ``buf.check()`` before using the result for an optimiser step.
     """
     lib = _lib.require()
     if multicast is None:
-        multicast = buf.has_multicast and buf.world > 2
+        multicast = buf.has_multicast and buf.world > 2 and \
+            os.environ.get('TGB_ALLREDUCE_NVLS', '0') == '1'
     if multicast and not buf.has_multicast:
         raise RuntimeError('multicast requested but this buffer has no multicast mapping')
     if cast_out is not None:

@@ -61,3 +61,9 @@ class GradientBucket:
         if scale != 1.0:
             self.flat.mul_(scale)
         return self.flat
+
+    def check(self) -> None:
+        """Raises if the fused all-reduce of this bucket timed out (see ``SymmetricBuffer.check``);
+        a no-op on the NCCL fallback, whose own watchdog reports failures."""
+        if self.symmetric is not None:
+            self.symmetric.check()

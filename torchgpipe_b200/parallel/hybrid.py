@@ -42,7 +42,8 @@ class HybridPipeline:
 
     def __init__(self, module: nn.Sequential, balance: Iterable[int], chunks: int,
                  layout: HybridLayout, device: torch.device, *, checkpoint: str = 'except_last',
-                 cuda_graphs: bool = False, use_symmetric: bool = True) -> None:
+                 cuda_graphs: bool = False, use_symmetric: bool = True,
+                 check_allreduce: bool = True) -> None:
         from torchgpipe_b200.distributed import DistributedGPipe, ProcessGroupTransport
         self.layout = layout
         workers = {s: f'replica{layout.replica}-stage{s}' for s in range(layout.stages)}
@@ -52,6 +53,9 @@ class HybridPipeline:
                                      cuda_graphs=cuda_graphs)
         self.bucket = GradientBucket(self.pipe.model().parameters(), layout.dp_group,
                                      use_symmetric=use_symmetric)
+        #: verify after every all-reduce that no replica timed out (one host sync per step, at
+        #: the point where the optimiser needs the reduced gradients anyway)
+        self.check_allreduce = check_allreduce
 
     def model(self) -> nn.Sequential:
         return self.pipe.model()
@@ -63,6 +67,8 @@ class HybridPipeline:
         """Backward of this stage for all micro-batches, then the stage's gradient all-reduce."""
         self.pipe.backward(losses)
         self.bucket.allreduce()
+        if self.check_allreduce:
+            self.bucket.check()
 
     def zero_grad(self) -> None:
         self.bucket.zero()

@@ -38,12 +38,18 @@ from torch import Tensor, nn
 
 __all__ = ['GraphedStage']
 
-Signature = Tuple[Tuple[Tuple[int, ...], torch.dtype, bool, bool], ...]
+Signature = Tuple[object, ...]
 
 
-def _signature(inputs: Sequence[Tensor]) -> Signature:
-    return tuple((tuple(t.shape), t.dtype, t.requires_grad,
-                  t.dim() == 4 and not t.is_contiguous()) for t in inputs)
+def _signature(inputs: Sequence[Tensor], module: Optional[nn.Module] = None,
+               grad: Optional[bool] = None) -> Signature:
+    """Key of one capture. Besides the tensors' shape / dtype / layout it holds everything that
+    changes WHICH kernels the stage function issues: ``module.training`` (Dropout, BatchNorm
+    batch-vs-running statistics) and the grad mode (a no-grad forward records no backward)."""
+    mode = (bool(module.training) if module is not None else True,
+            torch.is_grad_enabled() if grad is None else bool(grad))
+    return (mode,) + tuple((tuple(t.shape), t.dtype, t.requires_grad,
+                            t.dim() == 4 and not t.is_contiguous()) for t in inputs)
 
 
 class _Captured:
@@ -94,7 +100,7 @@ class GraphedStage:
         self.recomputes_skipped = 0
 
     # -- capture ---------------------------------------------------------------
-    def _capture(self, inputs: Sequence[Tensor]) -> _Captured:
+    def _capture(self, inputs: Sequence[Tensor], grad: bool = True) -> _Captured:
         from torchgpipe_b200 import ops
         cap = _Captured()
         with torch.cuda.device(self.device):
@@ -119,7 +125,7 @@ class GraphedStage:
             side.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(side):
                 for _ in range(self.warmup):
-                    with torch.enable_grad():
+                    with torch.set_grad_enabled(grad):
                         outs = self.function(tuple(cap.static_inputs))
                     gouts = [torch.ones_like(o) if o.requires_grad else None for o in outs]
                     run_backward(outs, gouts)
@@ -134,7 +140,7 @@ class GraphedStage:
 
             before = ops.launch_count()
             with torch.cuda.graph(cap.fwd, pool=self._pool):
-                with torch.enable_grad():
+                with torch.set_grad_enabled(grad):
                     cap.static_outputs = tuple(self.function(tuple(cap.static_inputs)))
             cap.native_launches_fwd = ops.launch_count() - before
 
@@ -154,11 +160,13 @@ class GraphedStage:
                 cap.static_grad_params = list(grads[n_in:])
         return cap
 
-    def _get(self, inputs: Sequence[Tensor]) -> _Captured:
-        sig = _signature(inputs)
+    def _get(self, inputs: Sequence[Tensor], grad: Optional[bool] = None) -> _Captured:
+        if grad is None:
+            grad = torch.is_grad_enabled()
+        sig = _signature(inputs, self.module, grad)
         cap = self._captured.get(sig)
         if cap is None:
-            cap = self._capture(inputs)
+            cap = self._capture(inputs, grad)
             self._captured[sig] = cap
         return cap
 
@@ -197,7 +205,7 @@ class GraphedStage:
         Parameter gradients are accumulated into ``param.grad``; the gradients of the inputs
         that require grad are returned (``None`` for the others).
         """
-        cap = self._get(inputs)
+        cap = self._get(inputs, grad=True)      # only a capture made with grad on has a backward
         if cap.bwd is None:
             return [None for _ in inputs]
         resident = self._resident
