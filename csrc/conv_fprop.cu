@@ -1,7 +1,15 @@
-// Implicit-GEMM 2-D convolution forward (stride 1) for sm_100a: tcgen05.mma (TF32 in, FP32
-// accumulate in TMEM), operands staged by TMA, NHWC activations, KRSC weights.
+// Implicit-GEMM 2-D convolution forward for sm_100a: tcgen05.mma (TF32 in, FP32 accumulate in
+// TMEM), operands staged by TMA, NHWC activations, KRSC weights.
 //
-//   Y[n,ho,wo,k] = sum_{r,s,c} X[n, ho+r-pad_h, wo+s-pad_w, c] * Wt[k,r,s,c]
+//   Y[n,ho,wo,k] = sum_{r,s,c} X[n, sh*ho+r-pad_h, sw*wo+s-pad_w, c] * Wt[k,r,s,c]
+//
+// Strides: a tap offset a = r - pad_h splits into a = sh*q + p (0 <= p < sh). All output rows of
+// a tile then read input rows sh*(ho+q) + p, i.e. rows ho+q of the sub-image "rows congruent to p
+// mod sh" - a plain strided view of X with its own tensor map (base moved by p rows, row stride
+// times sh). There is one such view per (p_h, p_w) pair, at most four for stride 2, and a tap's
+// TMA box in its view looks exactly like a stride-1 box: same shared-memory layout, same MMAs,
+// zero fill outside the view = zero padding outside the image. Negative padding (a crop) falls
+// out of the same arithmetic.
 //
 // GEMM view: M = N*Ho*Wo output pixels, N = K output channels, reduction = R*S*C.
 // One CTA tile = 128 output pixels arranged as a BW x BH x BNB box of (w, h, n) x BN channels.
@@ -38,9 +46,15 @@ constexpr int kUmmaK = 8;           // tf32: 32 bytes per MMA
 constexpr int kEpiChunk = 32;       // columns per epilogue chunk (= one 128B row of Y)
 constexpr int kThreads = 256;
 
+__host__ __device__ inline int floor_div(int a, int b) {
+  const int q = a / b;
+  return (a % b != 0 && ((a < 0) != (b < 0))) ? q - 1 : q;
+}
+
 struct ConvGeom {
   int N, H, W, C, K;
   int R, S, pad_h, pad_w;
+  int stride_h, stride_w;
   int Ho, Wo;
   int BW, BH, BNB;                  // pixel box; rows_valid = BW*BH*BNB <= 128
   int tiles_w, tiles_h, tiles_n, tiles_k;
@@ -81,6 +95,9 @@ struct SmemLayout {
 template <int BN, int STAGES, bool HALO = false, bool RESW = false>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
+                       const __grid_constant__ CUtensorMap tmap_x1,
+                       const __grid_constant__ CUtensorMap tmap_x2,
+                       const __grid_constant__ CUtensorMap tmap_x3,
                        const __grid_constant__ CUtensorMap tmap_w,
                        const __grid_constant__ CUtensorMap tmap_y,
                        const ConvGeom g, float* __restrict__ stats) {
@@ -112,6 +129,13 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_x);
+    if (g.stride_h * g.stride_w > 1) {
+      tma_prefetch_desc(&tmap_x1);
+      if (g.stride_h * g.stride_w > 2) {
+        tma_prefetch_desc(&tmap_x2);
+        tma_prefetch_desc(&tmap_x3);
+      }
+    }
     tma_prefetch_desc(&tmap_w);
     tma_prefetch_desc(&tmap_y);
   }
@@ -195,11 +219,18 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
         for (int it = it_begin; it < it_end; ++it) {
           const int r = tap / g.S;
           const int s = tap - r * g.S;
+          // tap offset = stride * q + p: box origin moves by q inside the parity-p view of X
+          const int ar = r - g.pad_h, as = s - g.pad_w;
+          const int qr = floor_div(ar, g.stride_h), qs = floor_div(as, g.stride_w);
+          const int view = (ar - qr * g.stride_h) * g.stride_w + (as - qs * g.stride_w);
+          const CUtensorMap* mx = view == 0 ? &tmap_x : view == 1 ? &tmap_x1
+                                : view == 2 ? &tmap_x2 : &tmap_x3;
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* a_dst = smem + stage * L::kStageBytes;
           uint8_t* b_dst = a_dst + L::kABytes;
           mbar_expect_tx(&full_bar[stage], stage_tx);
-          tma_load_4d(a_dst, &tmap_x, &full_bar[stage], cb * kBlockK, w0 + s, h0 + r, n0);
+          tma_load_4d(a_dst, mx, &full_bar[stage], cb * kBlockK, tw * g.BW + qs,
+                      th * g.BH + qr, n0);
           tma_load_4d(b_dst, &tmap_w, &full_bar[stage], cb * kBlockK, tap, k0, 0);
           if (++stage == STAGES) {
             stage = 0;
@@ -454,8 +485,12 @@ static void choose_pixel_box(int N, int Ho, int Wo, int stats_mode, int& BW, int
   }
 }
 
+struct XMaps {
+  CUtensorMap m[4];
+};
+
 template <int BN, int STAGES, bool HALO = false, bool RESW = false>
-static int launch_fprop(const CUtensorMap& mx, const CUtensorMap& mw, const CUtensorMap& my,
+static int launch_fprop(const XMaps& mx, const CUtensorMap& mw, const CUtensorMap& my,
                         const ConvGeom& g, float* stats, int sm_count, cudaStream_t stream) {
   using L = SmemLayout<BN, STAGES, HALO, RESW>;
   constexpr int smem_bytes = L::kTotal + 1024;      // + alignment slack
@@ -476,7 +511,8 @@ static int launch_fprop(const CUtensorMap& mx, const CUtensorMap& mw, const CUte
   }
   const int num_tiles = g.tiles_w * g.tiles_h * g.tiles_n * g.tiles_k * g.splits;
   const int grid = num_tiles < sm_count ? num_tiles : sm_count;
-  kern<<<grid, kThreads, smem_bytes, stream>>>(mx, mw, my, g, stats);
+  kern<<<grid, kThreads, smem_bytes, stream>>>(mx.m[0], mx.m[1], mx.m[2], mx.m[3], mw, my, g,
+                                               stats);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return set_error("conv_fprop launch: %s", cudaGetErrorString(e));
   count_launch();
@@ -486,15 +522,25 @@ static int launch_fprop(const CUtensorMap& mx, const CUtensorMap& mw, const CUte
 // Everything that is decided on the host before a launch: tile shapes, kernel variant, split of
 // the reduction. Shared by the launcher and by tgb_conv2d_fprop_plan (which lets callers and the
 // CPU test-suite see the decisions without a GPU). `stats_mode` is the effective mode (0 when no
-// statistics buffer is given).
+// statistics buffer is given). Ho / Wo <= 0: derive the output extent from the convolution
+// arithmetic; otherwise compute exactly that extent (data-gradient launches ask for the extent
+// of one output-parity class). `allow_split`: the split-K path zero-fills and reduce-adds into Y
+// and so needs a dense Y.
 static int plan_fprop(int N, int H, int W, int C, int K, int R, int S, int pad_h, int pad_w,
+                      int stride_h, int stride_w, int Ho, int Wo, bool allow_split,
                       int stats_mode, ConvGeom& g, int& BN_out, bool& halo_out,
                       bool& resident_out) {
+  if (stride_h < 1 || stride_w < 1 || stride_h * stride_w > 4)
+    return set_error("conv_fprop: strides up to 2x2 (or 1x4 / 4x1) are supported, got %dx%d",
+                     stride_h, stride_w);
   g.N = N; g.H = H; g.W = W; g.C = C; g.K = K;
   g.R = R; g.S = S; g.pad_h = pad_h; g.pad_w = pad_w;
-  g.Ho = H + 2 * pad_h - R + 1;
-  g.Wo = W + 2 * pad_w - S + 1;
-  if (g.Ho <= 0 || g.Wo <= 0) return set_error("conv_fprop: empty output");
+  g.stride_h = stride_h; g.stride_w = stride_w;
+  g.Ho = Ho > 0 ? Ho : (H + 2 * pad_h - R) / stride_h + 1;
+  g.Wo = Wo > 0 ? Wo : (W + 2 * pad_w - S) / stride_w + 1;
+  if (g.Ho <= 0 || g.Wo <= 0 || (Ho <= 0 && H + 2 * pad_h < R) || (Wo <= 0 && W + 2 * pad_w < S))
+    return set_error("conv_fprop: empty output");
+  const bool unit_stride = stride_h == 1 && stride_w == 1;
   choose_pixel_box(N, g.Ho, g.Wo, stats_mode, g.BW, g.BH, g.BNB);
   // Output-channel tile: the widest of {256,128,64,32} that wastes at most 1/8 of its columns.
   // A partial last tile is fine: weight rows past K are zero-filled by TMA and the store of
@@ -508,7 +554,7 @@ static int plan_fprop(int N, int H, int W, int C, int K, int R, int S, int pad_h
   // input: use the haloed-tile variant (8 x 16 pixel tiles, input read once per tile) when the
   // filter is at most 3x3, the image tiles well into 8 x 16 boxes and there are plenty of tiles.
   bool halo = false;
-  if (BN <= 64 && R <= 3 && S <= 3 && R * S > 1) {
+  if (BN <= 64 && R <= 3 && S <= 3 && R * S > 1 && unit_stride && pad_h >= 0 && pad_w >= 0) {
     const long tw8 = (g.Wo + kHaloW - 1) / kHaloW, th16 = (g.Ho + kHaloH - 1) / kHaloH;
     const double useful = static_cast<double>(g.Ho) * g.Wo / (tw8 * kHaloW * th16 * kHaloH);
     halo = useful >= 0.85 && tw8 * th16 * N * ((K + BN - 1) / BN) >= 4L * sm_count();
@@ -535,7 +581,7 @@ static int plan_fprop(int N, int H, int W, int C, int K, int R, int S, int pad_h
   const int base_tiles = g.tiles_w * g.tiles_h * g.tiles_n * g.tiles_k;
   const int k_iters = halo ? g.c_blocks : R * S * g.c_blocks;
   g.splits = 1;
-  if (!halo && k_iters >= 32 && getenv("TGB_FPROP_NOSPLIT") == nullptr) {
+  if (!halo && allow_split && k_iters >= 32 && getenv("TGB_FPROP_NOSPLIT") == nullptr) {
     // Wave model: `items` equal work items run in ceil(items / sms) waves; an item costs its
     // reduction iterations plus an epilogue worth about kEpi iterations. Splitting the reduction
     // s ways shortens the items and fills partial waves (90 tiles on 148 SMs leave 39 % of the
@@ -572,6 +618,131 @@ static int plan_fprop(int N, int H, int W, int C, int K, int R, int S, int pad_h
   return 0;
 }
 
+// A convolution with explicit addressing of X and Y (all strides in elements):
+//   X[n][h][w][c] at x + n*x_sn + h*x_sh + w*x_sw + c,  0 <= h < H, 0 <= w < W, 0 <= c < C
+//   Y[n][ho][wo][k] at y + n*y_sn + ho*y_sh + wo*y_sw + k
+// Dense NHWC is (C, W*C, H*W*C). Other choices serve the data gradient of a strided convolution
+// (Y = the pixels of one parity class of dX), channel-offset outputs (concatenation for free:
+// y_sw larger than K) and the packed small-channel stem (x_sw smaller than C: every "pixel" is a
+// window of several real pixels, see tgb_conv2d_stem_*).
+struct ConvProblem {
+  const float* x; const float* w; float* y; float* stats;
+  int N, H, W, C, K, R, S, pad_h, pad_w, stride_h, stride_w;
+  int Ho, Wo;                       // <= 0: from the convolution arithmetic
+  long long x_sw, x_sh, x_sn;
+  long long y_sw, y_sh, y_sn;
+  int stats_mode;
+};
+
+static int run_fprop(const ConvProblem& p, cudaStream_t stream) {
+  if (p.C % 4 != 0 || p.K % 4 != 0)
+    return set_error("conv_fprop: need C %% 4 == 0 and K %% 4 == 0 (got C=%d K=%d)", p.C, p.K);
+  if ((reinterpret_cast<uintptr_t>(p.x) | reinterpret_cast<uintptr_t>(p.w) |
+       reinterpret_cast<uintptr_t>(p.y)) & 15)
+    return set_error("conv_fprop: tensors must be 16-byte aligned");
+  if ((p.x_sw | p.x_sh | p.x_sn | p.y_sw | p.y_sh | p.y_sn) & 3)
+    return set_error("conv_fprop: strides must be multiples of 4 elements (16 bytes)");
+  ConvGeom g;
+  int BN = 32;
+  bool halo = false, resident = false;
+  const int Ho_dense = (p.H + 2 * p.pad_h - p.R) / p.stride_h + 1;
+  const int Wo_dense = (p.W + 2 * p.pad_w - p.S) / p.stride_w + 1;
+  const int Ho = p.Ho > 0 ? p.Ho : Ho_dense, Wo = p.Wo > 0 ? p.Wo : Wo_dense;
+  const bool y_dense = p.y_sw == p.K && p.y_sh == static_cast<long long>(Wo) * p.K &&
+                       p.y_sn == static_cast<long long>(Ho) * Wo * p.K;
+  if (int rc = plan_fprop(p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.pad_h, p.pad_w, p.stride_h,
+                          p.stride_w, p.Ho, p.Wo, y_dense, p.stats ? p.stats_mode : 0, g, BN,
+                          halo, resident))
+    return rc;
+  const int sms = sm_count();
+  const bool stats_after = g.splits > 1 && g.stats_mode != 0;
+  const int stats_mode_req = g.stats_mode;
+  if (g.splits > 1) {
+    g.stats_mode = 0;         // partial tiles cannot produce sum of squares: tgb_moments below
+    cudaError_t e = cudaMemsetAsync(p.y, 0, static_cast<size_t>(p.N) * g.Ho * g.Wo * p.K * 4,
+                                    stream);
+    if (e != cudaSuccess) return set_error("conv_fprop: memset: %s", cudaGetErrorString(e));
+  }
+
+  XMaps mx;
+  CUtensorMap mw, my;
+  const int views = p.stride_h * p.stride_w;
+  for (int v = 0; v < 4; ++v) {
+    // view (ph, pw): the pixels with h = stride_h*hh + ph, w = stride_w*ww + pw. Views past
+    // `views` are never touched by the kernel; give them the geometry of view 0.
+    const int ph = v < views ? v / p.stride_w : 0, pw = v < views ? v % p.stride_w : 0;
+    const long long Hv = (p.H - ph + p.stride_h - 1) / p.stride_h;
+    const long long Wv = (p.W - pw + p.stride_w - 1) / p.stride_w;
+    if (Hv <= 0 || Wv <= 0) {               // a parity class without pixels (1-pixel images)
+      mx.m[v] = mx.m[0];
+      continue;
+    }
+    uint64_t dims[4] = {(uint64_t)p.C, (uint64_t)Wv, (uint64_t)Hv, (uint64_t)p.N};
+    uint64_t strides[3] = {(uint64_t)(p.x_sw * p.stride_w) * 4,
+                           (uint64_t)(p.x_sh * p.stride_h) * 4, (uint64_t)p.x_sn * 4};
+    uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
+    if (halo) {               // the input tile with its halo in one box
+      box[1] = (uint32_t)(g.BW + p.S - 1);
+      box[2] = (uint32_t)(g.BH + p.R - 1);
+    }
+    if (make_tensor_map(&mx.m[v], p.x + ph * p.x_sh + pw * p.x_sw, 4, 4, dims, strides, box, 1))
+      return set_error("conv_fprop: tensor map for X (view %d) failed", v);
+  }
+  {
+    // weights [K][R*S][C] viewed as a 3-D (4-D with a unit dim) tensor so that a partial last
+    // channel block is zero-filled instead of bleeding into the next tap
+    uint64_t dims[4] = {(uint64_t)p.C, (uint64_t)(p.R * p.S), (uint64_t)p.K, 1};
+    uint64_t strides[3] = {(uint64_t)p.C * 4, (uint64_t)p.R * p.S * p.C * 4,
+                           (uint64_t)p.K * p.R * p.S * p.C * 4};
+    uint32_t box[4] = {32, 1, (uint32_t)BN, 1};
+    if (make_tensor_map(&mw, p.w, 4, 4, dims, strides, box, 1))
+      return set_error("conv_fprop: tensor map for W failed");
+  }
+  {
+    uint64_t dims[4] = {(uint64_t)p.K, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)p.N};
+    uint64_t strides[3] = {(uint64_t)p.y_sw * 4, (uint64_t)p.y_sh * 4, (uint64_t)p.y_sn * 4};
+    uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
+    if (make_tensor_map(&my, p.y, 4, 4, dims, strides, box, 1))
+      return set_error("conv_fprop: tensor map for Y failed");
+  }
+  int rc;
+  if (halo && resident) {
+    rc = BN == 64 ? launch_fprop<64, 2, true, true>(mx, mw, my, g, p.stats, sms, stream)
+                  : launch_fprop<32, 2, true, true>(mx, mw, my, g, p.stats, sms, stream);
+  } else if (halo) {
+    rc = BN == 64 ? launch_fprop<64, 2, true>(mx, mw, my, g, p.stats, sms, stream)
+                  : launch_fprop<32, 3, true>(mx, mw, my, g, p.stats, sms, stream);
+  } else
+  switch (BN) {
+    case 256: rc = launch_fprop<256, 4>(mx, mw, my, g, p.stats, sms, stream); break;
+    case 128: rc = launch_fprop<128, 6>(mx, mw, my, g, p.stats, sms, stream); break;
+    case 64:  rc = launch_fprop<64, 8>(mx, mw, my, g, p.stats, sms, stream); break;
+    default:  rc = launch_fprop<32, 8>(mx, mw, my, g, p.stats, sms, stream); break;
+  }
+  if (rc == 0 && stats_after) {
+    // Y is [N][Ho*Wo][K]: per-image (mode 1) or per-channel (mode 2) moments in one more pass
+    rc = stats_mode_req == 1 ? tgb_moments(p.y, p.stats, p.N, g.Ho * g.Wo, p.K, stream)
+                             : tgb_moments(p.y, p.stats, 1, p.N * g.Ho * g.Wo, p.K, stream);
+  }
+  return rc;
+}
+
+static ConvProblem dense_problem(const float* x, const float* w, float* y, float* stats, int N,
+                                 int H, int W, int C, int K, int R, int S, int pad_h, int pad_w,
+                                 int stride_h, int stride_w, int stats_mode) {
+  ConvProblem p;
+  p.x = x; p.w = w; p.y = y; p.stats = stats;
+  p.N = N; p.H = H; p.W = W; p.C = C; p.K = K; p.R = R; p.S = S;
+  p.pad_h = pad_h; p.pad_w = pad_w; p.stride_h = stride_h; p.stride_w = stride_w;
+  p.Ho = p.Wo = 0;
+  p.x_sw = C; p.x_sh = static_cast<long long>(W) * C; p.x_sn = static_cast<long long>(H) * W * C;
+  const long long Ho = (H + 2 * pad_h - R) / (stride_h > 0 ? stride_h : 1) + 1;
+  const long long Wo = (W + 2 * pad_w - S) / (stride_w > 0 ? stride_w : 1) + 1;
+  p.y_sw = K; p.y_sh = Wo * K; p.y_sn = Ho * Wo * K;
+  p.stats_mode = stats_mode;
+  return p;
+}
+
 }  // namespace tgb
 
 using namespace tgb;
@@ -579,75 +750,179 @@ using namespace tgb;
 extern "C" int tgb_conv2d_fprop_tf32(const float* x, const float* w, float* y, float* stats,
                                      int N, int H, int W, int C, int K, int R, int S, int pad_h,
                                      int pad_w, int stats_mode, cudaStream_t stream) {
-  if (C % 4 != 0 || K % 4 != 0)
-    return set_error("conv_fprop: need C %% 4 == 0 and K %% 4 == 0 (got C=%d K=%d)", C, K);
-  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) |
-       reinterpret_cast<uintptr_t>(y)) & 15)
-    return set_error("conv_fprop: tensors must be 16-byte aligned");
-  ConvGeom g;
-  int BN = 32;
-  bool halo = false, resident = false;
-  if (int rc = plan_fprop(N, H, W, C, K, R, S, pad_h, pad_w, stats ? stats_mode : 0, g, BN, halo,
-                          resident))
-    return rc;
-  const int sms = sm_count();
-  const bool stats_after = g.splits > 1 && g.stats_mode != 0;
-  const int stats_mode_req = g.stats_mode;
-  if (g.splits > 1) {
-    g.stats_mode = 0;         // partial tiles cannot produce sum of squares: tgb_moments below
-    cudaError_t e = cudaMemsetAsync(y, 0, static_cast<size_t>(N) * g.Ho * g.Wo * K * 4, stream);
-    if (e != cudaSuccess) return set_error("conv_fprop: memset: %s", cudaGetErrorString(e));
-  }
+  return run_fprop(dense_problem(x, w, y, stats, N, H, W, C, K, R, S, pad_h, pad_w, 1, 1,
+                                 stats_mode), stream);
+}
 
-  CUtensorMap mx, mw, my;
-  {
-    uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
-    uint64_t strides[3] = {(uint64_t)C * 4, (uint64_t)W * C * 4, (uint64_t)H * W * C * 4};
-    uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
-    if (halo) {               // the input tile with its halo in one box
-      box[1] = (uint32_t)(g.BW + S - 1);
-      box[2] = (uint32_t)(g.BH + R - 1);
+extern "C" int tgb_conv2d_fprop_strided_tf32(const float* x, const float* w, float* y,
+                                             float* stats, int N, int H, int W, int C, int K,
+                                             int R, int S, int pad_h, int pad_w, int stride_h,
+                                             int stride_w, int Ho, int Wo,
+                                             long long y_pixel_stride, int stats_mode,
+                                             cudaStream_t stream) {
+  if (stride_h < 1 || stride_w < 1) return set_error("conv_fprop: strides must be positive");
+  ConvProblem p = dense_problem(x, w, y, stats, N, H, W, C, K, R, S, pad_h, pad_w, stride_h,
+                                stride_w, stats_mode);
+  // Ho / Wo > 0: the caller fixes the output extent (asymmetric padding: with pad = -1 and the
+  // extent of the unshifted convolution, the far edge is padded with zeros by TMA)
+  long long ho = p.y_sn / p.y_sh, wo = p.y_sh / K;
+  if (Ho > 0) { p.Ho = Ho; ho = Ho; }
+  if (Wo > 0) { p.Wo = Wo; wo = Wo; }
+  if (y_pixel_stride <= 0) y_pixel_stride = K;
+  // y_pixel_stride > K: Y is a channel slice of a wider NHWC tensor (part of a concatenation)
+  if (y_pixel_stride < K) return set_error("conv_fprop: y_pixel_stride smaller than K");
+  p.y_sw = y_pixel_stride; p.y_sh = wo * y_pixel_stride; p.y_sn = ho * wo * y_pixel_stride;
+  return run_fprop(p, stream);
+}
+
+// ---- small-channel stem on the packed buffer of tgb_stem_pack (see conv_small.cu) ------------
+// xp: [N][Hp][Wp][4] zero-haloed image; wv: [K][R][32] with wv[k][r][4*s+c] = W[k][c][r][s]
+// (zero where s >= S or c >= C). The convolution is R x 1 over the 32-"channel" window view.
+extern "C" int tgb_conv2d_stem_fprop_tf32(const float* xp, const float* wv, float* y,
+                                          float* stats, int N, int Hp, int Wp, int K, int R,
+                                          int stride_h, int stride_w, int stats_mode,
+                                          cudaStream_t stream) {
+  if (Wp < 8) return set_error("stem_fprop: packed rows must hold at least one 8-pixel window");
+  ConvProblem p = dense_problem(xp, wv, y, stats, N, Hp, Wp - 7, 32, K, R, 1, 0, 0, stride_h,
+                                stride_w, stats_mode);
+  p.x_sw = 4;                                   // next window starts one pixel (4 floats) later
+  p.x_sh = static_cast<long long>(Wp) * 4;
+  p.x_sn = static_cast<long long>(Hp) * Wp * 4;
+  return run_fprop(p, stream);
+}
+
+// ---- data gradient of a (possibly strided) convolution -------------------------------------
+//   dX[n,h,w,c] = sum over (r,s,k) with (h+pad_h-r) % sh == 0 and (w+pad_w-s) % sw == 0 of
+//                 dY[n,(h+pad_h-r)/sh,(w+pad_w-s)/sw,k] * W[k,r,s,c]
+// For the input pixels of one parity class (h = sh*hh + a, w = sw*ww + b) only the filter rows
+// r = r0 + sh*j (r0 = (a+pad_h) mod sh) take part, and the sum becomes a stride-1 correlation of
+// dY with that sub-filter: one launch of the forward kernel per class, its output tensor map
+// being the strided view "pixels of class (a,b)" of dX. The sub-filters, tap-flipped and
+// channel-transposed, are prepared by tgb_dgrad_weight_strided (class-major, [C][Rj*Si][K] each).
+struct DgradClass {
+  int r0, Rj, dh, s0, Si, dw;
+  long long w_offset;         // elements from the start of the class-major weight buffer
+};
+
+static void dgrad_classes(int C, int K, int R, int S, int pad_h, int pad_w, int sh, int sw,
+                          DgradClass* cls, long long* total) {
+  long long off = 0;
+  for (int a = 0; a < sh; ++a)
+    for (int b = 0; b < sw; ++b) {
+      DgradClass& c = cls[a * sw + b];
+      c.r0 = ((a + pad_h) % sh + sh) % sh;
+      c.s0 = ((b + pad_w) % sw + sw) % sw;
+      c.Rj = c.r0 < R ? (R - c.r0 + sh - 1) / sh : 0;
+      c.Si = c.s0 < S ? (S - c.s0 + sw - 1) / sw : 0;
+      c.dh = (a + pad_h - c.r0) / sh;
+      c.dw = (b + pad_w - c.s0) / sw;
+      c.w_offset = off;
+      off += static_cast<long long>(C) * c.Rj * c.Si * K;
     }
-    if (make_tensor_map(&mx, x, 4, 4, dims, strides, box, 1))
-      return set_error("conv_fprop: tensor map for X failed");
+  *total = off;
+}
+
+extern "C" long long tgb_dgrad_weight_strided_elems(int K, int C, int R, int S, int pad_h,
+                                                    int pad_w, int stride_h, int stride_w) {
+  if (stride_h < 1 || stride_w < 1 || stride_h * stride_w > 4) return -1;
+  DgradClass cls[4];
+  long long total = 0;
+  dgrad_classes(C, K, R, S, pad_h, pad_w, stride_h, stride_w, cls, &total);
+  return total;
+}
+
+__global__ void dgrad_weight_class_kernel(const float* __restrict__ w, float* __restrict__ out,
+                                          int K, int C, int R, int S, int r0, int Rj, int s0,
+                                          int Si, int sh, int sw) {
+  // out[c][j'][i'][k] = w[k][r0 + sh*(Rj-1-j')][s0 + sw*(Si-1-i')][c]; a 32x32 (k, c) tile goes
+  // through shared memory so that both the read (c fastest) and the write (k fastest) coalesce
+  __shared__ float tile[32][33];
+  const int tap = blockIdx.z;
+  const int jp = tap / Si, ip = tap - jp * Si;
+  const int r = r0 + sh * (Rj - 1 - jp), s = s0 + sw * (Si - 1 - ip);
+  const int k0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int k = k0 + i, c = c0 + threadIdx.x;
+    tile[i][threadIdx.x] = (k < K && c < C)
+        ? w[((static_cast<size_t>(k) * R + r) * S + s) * C + c] : 0.f;
   }
-  {
-    // weights [K][R*S][C] viewed as a 3-D (4-D with a unit dim) tensor so that a partial last
-    // channel block is zero-filled instead of bleeding into the next tap
-    uint64_t dims[4] = {(uint64_t)C, (uint64_t)(R * S), (uint64_t)K, 1};
-    uint64_t strides[3] = {(uint64_t)C * 4, (uint64_t)R * S * C * 4, (uint64_t)K * R * S * C * 4};
-    uint32_t box[4] = {32, 1, (uint32_t)BN, 1};
-    if (make_tensor_map(&mw, w, 4, 4, dims, strides, box, 1))
-      return set_error("conv_fprop: tensor map for W failed");
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, k = k0 + threadIdx.x;
+    if (c < C && k < K)
+      out[(static_cast<size_t>(c) * Rj * Si + tap) * K + k] = tile[threadIdx.x][i];
   }
-  {
-    uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)N};
-    uint64_t strides[3] = {(uint64_t)K * 4, (uint64_t)g.Wo * K * 4,
-                           (uint64_t)g.Ho * g.Wo * K * 4};
-    uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
-    if (make_tensor_map(&my, y, 4, 4, dims, strides, box, 1))
-      return set_error("conv_fprop: tensor map for Y failed");
+}
+
+extern "C" int tgb_dgrad_weight_strided(const float* w, float* out, int K, int C, int R, int S,
+                                        int pad_h, int pad_w, int stride_h, int stride_w,
+                                        cudaStream_t stream) {
+  if (stride_h < 1 || stride_w < 1 || stride_h * stride_w > 4)
+    return set_error("dgrad_weight_strided: unsupported stride %dx%d", stride_h, stride_w);
+  DgradClass cls[4];
+  long long total = 0;
+  dgrad_classes(C, K, R, S, pad_h, pad_w, stride_h, stride_w, cls, &total);
+  for (int v = 0; v < stride_h * stride_w; ++v) {
+    const DgradClass& c = cls[v];
+    if (c.Rj * c.Si == 0) continue;
+    dim3 grid((K + 31) / 32, (C + 31) / 32, c.Rj * c.Si), block(32, 8);
+    dgrad_weight_class_kernel<<<grid, block, 0, stream>>>(w, out + c.w_offset, K, C, R, S, c.r0,
+                                                          c.Rj, c.s0, c.Si, stride_h, stride_w);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error("dgrad_weight_strided launch: %s",
+                                           cudaGetErrorString(e));
+    count_launch();
   }
-  int rc;
-  if (halo && resident) {
-    rc = BN == 64 ? launch_fprop<64, 2, true, true>(mx, mw, my, g, stats, sms, stream)
-                  : launch_fprop<32, 2, true, true>(mx, mw, my, g, stats, sms, stream);
-  } else if (halo) {
-    rc = BN == 64 ? launch_fprop<64, 2, true>(mx, mw, my, g, stats, sms, stream)
-                  : launch_fprop<32, 3, true>(mx, mw, my, g, stats, sms, stream);
-  } else
-  switch (BN) {
-    case 256: rc = launch_fprop<256, 4>(mx, mw, my, g, stats, sms, stream); break;
-    case 128: rc = launch_fprop<128, 6>(mx, mw, my, g, stats, sms, stream); break;
-    case 64:  rc = launch_fprop<64, 8>(mx, mw, my, g, stats, sms, stream); break;
-    default:  rc = launch_fprop<32, 8>(mx, mw, my, g, stats, sms, stream); break;
+  return 0;
+}
+
+// dy_pixel_stride: elements between consecutive pixels of dY (K for a dense tensor, more when dY
+// is a channel slice of a wider NHWC gradient). keep_untouched != 0: input pixels that no filter
+// tap reads are left as they are instead of being zero-filled (two convolutions that read
+// disjoint pixel classes of one input - AmoebaNet's FactorizedReduce - write one dX in turn).
+extern "C" int tgb_conv2d_dgrad_tf32(const float* dy, const float* wt_classes, float* dx, int N,
+                                     int H, int W, int C, int K, int R, int S, int pad_h,
+                                     int pad_w, int stride_h, int stride_w, int Ho_given,
+                                     int Wo_given, long long dy_pixel_stride, int keep_untouched,
+                                     cudaStream_t stream) {
+  if (stride_h < 1 || stride_w < 1 || stride_h * stride_w > 4)
+    return set_error("conv_dgrad: unsupported stride %dx%d", stride_h, stride_w);
+  const int Ho = Ho_given > 0 ? Ho_given : (H + 2 * pad_h - R) / stride_h + 1;
+  const int Wo = Wo_given > 0 ? Wo_given : (W + 2 * pad_w - S) / stride_w + 1;
+  if (Ho <= 0 || Wo <= 0) return set_error("conv_dgrad: empty output");
+  DgradClass cls[4];
+  long long total = 0;
+  dgrad_classes(C, K, R, S, pad_h, pad_w, stride_h, stride_w, cls, &total);
+  const int views = stride_h * stride_w;
+  bool any_empty = false;
+  for (int v = 0; v < views; ++v) any_empty |= cls[v].Rj * cls[v].Si == 0;
+  if (dy_pixel_stride <= 0) dy_pixel_stride = K;
+  if (dy_pixel_stride < K || (dy_pixel_stride & 3))
+    return set_error("conv_dgrad: bad dy_pixel_stride %lld for K=%d", dy_pixel_stride, K);
+  if (any_empty && !keep_untouched) {   // pixels no filter tap ever reads (e.g. 1x1 stride 2)
+    cudaError_t e = cudaMemsetAsync(dx, 0, static_cast<size_t>(N) * H * W * C * 4, stream);
+    if (e != cudaSuccess) return set_error("conv_dgrad: memset: %s", cudaGetErrorString(e));
   }
-  if (rc == 0 && stats_after) {
-    // Y is [N][Ho*Wo][K]: per-image (mode 1) or per-channel (mode 2) moments in one more pass
-    rc = stats_mode_req == 1 ? tgb_moments(y, stats, N, g.Ho * g.Wo, K, stream)
-                             : tgb_moments(y, stats, 1, N * g.Ho * g.Wo, K, stream);
+  for (int v = 0; v < views; ++v) {
+    const DgradClass& c = cls[v];
+    const int a = v / stride_w, b = v % stride_w;
+    const int Hc = (H - a + stride_h - 1) / stride_h, Wc = (W - b + stride_w - 1) / stride_w;
+    if (c.Rj * c.Si == 0 || Hc <= 0 || Wc <= 0) continue;
+    ConvProblem p;
+    p.x = dy; p.w = wt_classes + c.w_offset; p.stats = nullptr; p.stats_mode = 0;
+    p.y = dx + (static_cast<long long>(a) * W + b) * C;
+    p.N = N; p.H = Ho; p.W = Wo; p.C = K; p.K = C; p.R = c.Rj; p.S = c.Si;
+    p.pad_h = c.Rj - 1 - c.dh; p.pad_w = c.Si - 1 - c.dw;
+    p.stride_h = p.stride_w = 1;
+    p.Ho = Hc; p.Wo = Wc;
+    p.x_sw = dy_pixel_stride; p.x_sh = static_cast<long long>(Wo) * dy_pixel_stride;
+    p.x_sn = static_cast<long long>(Ho) * Wo * dy_pixel_stride;
+    p.y_sw = static_cast<long long>(stride_w) * C;
+    p.y_sh = static_cast<long long>(stride_h) * W * C;
+    p.y_sn = static_cast<long long>(H) * W * C;
+    if (int rc = run_fprop(p, stream)) return rc;
   }
-  return rc;
+  return 0;
 }
 
 // out[16]: BN, BW, BH, BNB, tiles_w, tiles_h, tiles_n, tiles_k, splits, iters_per_split, halo,
@@ -659,7 +934,8 @@ extern "C" int tgb_conv2d_fprop_plan(int N, int H, int W, int C, int K, int R, i
   ConvGeom g;
   int BN = 32;
   bool halo = false, resident = false;
-  if (int rc = plan_fprop(N, H, W, C, K, R, S, pad_h, pad_w, stats_mode, g, BN, halo, resident))
+  if (int rc = plan_fprop(N, H, W, C, K, R, S, pad_h, pad_w, 1, 1, 0, 0, true, stats_mode, g, BN,
+                          halo, resident))
     return rc;
   const int stages = halo ? (resident ? 2 : (BN == 64 ? 2 : 3))
                           : (BN == 256 ? 4 : BN == 128 ? 6 : 8);

@@ -1,6 +1,9 @@
-// Weight gradient of a stride-1 2-D convolution for sm_100a (tcgen05, TF32 -> FP32 in TMEM).
+// Weight gradient of a 2-D convolution for sm_100a (tcgen05, TF32 -> FP32 in TMEM).
 //
-//   dW[k,r,s,c] = sum_{n,ho,wo} dY[n,ho,wo,k] * X[n, ho+r-pad_h, wo+s-pad_w, c]
+//   dW[k,r,s,c] = sum_{n,ho,wo} dY[n,ho,wo,k] * X[n, sh*ho+r-pad_h, sw*wo+s-pad_w, c]
+//
+// Strides work as in conv_fprop.cu: a tap's X box is a stride-1 box inside the view of X that
+// holds the pixels of the tap's parity class (one tensor map per class).
 //
 // GEMM view per filter tap: M = K (output channels), N = C (input channels), and the reduction
 // runs over all N*Ho*Wo output pixels. In NHWC memory the reduction index is the *outer*
@@ -32,9 +35,15 @@ constexpr int kWgM = 128;
 constexpr int kWgChunkBytes = 4096;      // 32 pixels x 128 B: one channel chunk of one stage
 constexpr int kWgMaxPix = 32;
 
+__host__ __device__ inline int wg_floor_div(int a, int b) {
+  const int q = a / b;
+  return (a % b != 0 && ((a < 0) != (b < 0))) ? q - 1 : q;
+}
+
 struct WgradGeom {
   int N, H, W, C, K;
   int R, S, pad_h, pad_w;
+  int stride_h, stride_w;
   int Ho, Wo;
   int BW, BH, BNB, P;                    // pixel box, P = BW*BH*BNB (multiple of 8, <= 32)
   int tiles_w, tiles_h, tiles_n;         // pixel blocks
@@ -56,7 +65,10 @@ struct WgSmem {
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(kWgThreads, 1)
 conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmap_dy,
-                       const __grid_constant__ CUtensorMap tmap_x, const WgradGeom g,
+                       const __grid_constant__ CUtensorMap tmap_x,
+                       const __grid_constant__ CUtensorMap tmap_x1,
+                       const __grid_constant__ CUtensorMap tmap_x2,
+                       const __grid_constant__ CUtensorMap tmap_x3, const WgradGeom g,
                        float* __restrict__ out) {
   using L = WgSmem<BN, STAGES>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -114,6 +126,12 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmap_dy,
         int kt, ct, tap, split;
         decode(item, kt, ct, tap, split);
         const int r = tap / g.S, s = tap - r * g.S;
+        // tap offset = stride * q + p: a stride-1 box, q pixels in, of the parity-p view of X
+        const int ar = r - g.pad_h, as = s - g.pad_w;
+        const int qr = wg_floor_div(ar, g.stride_h), qs = wg_floor_div(as, g.stride_w);
+        const int view = (ar - qr * g.stride_h) * g.stride_w + (as - qs * g.stride_w);
+        const CUtensorMap* mx = view == 0 ? &tmap_x : view == 1 ? &tmap_x1
+                              : view == 2 ? &tmap_x2 : &tmap_x3;
         const int b_begin = split * g.blocks_per_split;
         const int b_end = min(total_blocks, b_begin + g.blocks_per_split);
         for (int blk = b_begin; blk < b_end; ++blk) {
@@ -132,8 +150,8 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmap_dy,
                         kt * kWgM + ch * 32, w0, h0, n0);
 #pragma unroll
           for (int ch = 0; ch < BN / 32; ++ch)
-            tma_load_4d(b_dst + ch * kWgChunkBytes, &tmap_x, &full_bar[stage],
-                        ct * BN + ch * 32, w0 + s - g.pad_w, h0 + r - g.pad_h, n0);
+            tma_load_4d(b_dst + ch * kWgChunkBytes, mx, &full_bar[stage],
+                        ct * BN + ch * 32, w0 + qs, h0 + qr, n0);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -301,7 +319,7 @@ static int wgrad_tma_swizzle() {
 }
 
 template <int BN, int STAGES>
-static int launch_wgrad(const CUtensorMap& mdy, const CUtensorMap& mx, const WgradGeom& g,
+static int launch_wgrad(const CUtensorMap& mdy, const CUtensorMap* mx, const WgradGeom& g,
                         float* out, int grid, cudaStream_t stream) {
   using L = WgSmem<BN, STAGES>;
   constexpr int smem_bytes = L::kTotal + 1024;
@@ -320,7 +338,7 @@ static int launch_wgrad(const CUtensorMap& mdy, const CUtensorMap& mx, const Wgr
                                            cudaGetErrorString(e));
     configured = true;
   }
-  kern<<<grid, kWgThreads, smem_bytes, stream>>>(mdy, mx, g, out);
+  kern<<<grid, kWgThreads, smem_bytes, stream>>>(mdy, mx[0], mx[1], mx[2], mx[3], g, out);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return set_error("conv_wgrad launch: %s", cudaGetErrorString(e));
   count_launch();
@@ -330,13 +348,19 @@ static int launch_wgrad(const CUtensorMap& mdy, const CUtensorMap& mx, const Wgr
 // Fills the geometry and the number of splits for a problem; shared by the planning query and
 // the launcher so both always agree.
 static int plan_wgrad(int N, int H, int W, int C, int K, int R, int S, int pad_h, int pad_w,
-                      WgradGeom& g, int& BN) {
+                      int stride_h, int stride_w, WgradGeom& g, int& BN, int Ho_given = 0,
+                      int Wo_given = 0) {
   if (C % 4 != 0 || K % 4 != 0) return set_error("conv_wgrad: need C %% 4 == 0 and K %% 4 == 0");
+  if (stride_h < 1 || stride_w < 1 || stride_h * stride_w > 4)
+    return set_error("conv_wgrad: unsupported stride %dx%d", stride_h, stride_w);
   g.N = N; g.H = H; g.W = W; g.C = C; g.K = K;
   g.R = R; g.S = S; g.pad_h = pad_h; g.pad_w = pad_w;
-  g.Ho = H + 2 * pad_h - R + 1;
-  g.Wo = W + 2 * pad_w - S + 1;
-  if (g.Ho <= 0 || g.Wo <= 0) return set_error("conv_wgrad: empty output");
+  g.stride_h = stride_h; g.stride_w = stride_w;
+  g.Ho = Ho_given > 0 ? Ho_given : (H + 2 * pad_h - R) / stride_h + 1;
+  g.Wo = Wo_given > 0 ? Wo_given : (W + 2 * pad_w - S) / stride_w + 1;
+  if (g.Ho <= 0 || g.Wo <= 0 || (Ho_given <= 0 && H + 2 * pad_h < R) ||
+      (Wo_given <= 0 && W + 2 * pad_w < S))
+    return set_error("conv_wgrad: empty output");
   choose_wgrad_box(N, g.Ho, g.Wo, g.BW, g.BH, g.BNB);
   g.P = g.BW * g.BH * g.BNB;
   g.tiles_w = (g.Wo + g.BW - 1) / g.BW;
@@ -394,79 +418,122 @@ static int choose_wgrad_kernel(int N, int Ho, int Wo, int C, int S) {
   return wgrad_fused_preferred(N, Ho, Wo, C, S) ? 1 : 0;
 }
 
-extern "C" long long tgb_conv2d_wgrad_scratch_bytes(int N, int H, int W, int C, int K, int R,
-                                                    int S, int pad_h, int pad_w) {
+namespace tgb {
+
+// Explicit addressing (strides in elements), as ConvProblem in conv_fprop.cu:
+//   X[n][h][w][c]   at x  + n*x_sn + h*x_sh + w*x_sw + c
+//   dY[n][ho][wo][k] at dy + (n*Ho*Wo + ho*Wo + wo) * dy_sw + k   (dy_sw > K: a channel slice)
+struct WgradProblem {
+  const float* dy; const float* x; float* dw; float* scratch; long long scratch_bytes;
+  int N, H, W, C, K, R, S, pad_h, pad_w, stride_h, stride_w;
+  long long x_sw, x_sh, x_sn, dy_sw;
+  int accumulate;
+  int Ho = 0, Wo = 0;               // > 0: output extent fixed by the caller (asymmetric padding)
+};
+
+static bool wgrad_is_plain(const WgradProblem& p) {
+  return p.stride_h == 1 && p.stride_w == 1 && p.x_sw == p.C &&
+         p.x_sh == static_cast<long long>(p.W) * p.C &&
+         p.x_sn == static_cast<long long>(p.H) * p.W * p.C && p.dy_sw == p.K;
+}
+
+static long long wgrad_scratch_need(int N, int H, int W, int C, int K, int R, int S, int pad_h,
+                                    int pad_w, int stride_h, int stride_w, bool plain,
+                                    int Ho_given = 0, int Wo_given = 0) {
   if (C % 4 != 0 || K % 4 != 0) {
     set_error("conv_wgrad: need C %% 4 == 0 and K %% 4 == 0");
     return -1;
   }
+  if (stride_h < 1 || stride_w < 1) {
+    set_error("conv_wgrad: strides must be positive");
+    return -1;
+  }
   int splits;
-  const int Wo = W + 2 * pad_w - S + 1, Ho = H + 2 * pad_h - R + 1;
+  const int Wo = Wo_given > 0 ? Wo_given : (W + 2 * pad_w - S) / stride_w + 1;
+  const int Ho = Ho_given > 0 ? Ho_given : (H + 2 * pad_h - R) / stride_h + 1;
   int BN;
-  if (choose_wgrad_kernel(N, Ho, Wo, C, S)) {
+  plain = plain && Ho_given <= 0 && Wo_given <= 0;
+  if (plain && choose_wgrad_kernel(N, Ho, Wo, C, S)) {
     WgradFusedGeom g;
     if (plan_wgrad_fused(N, H, W, C, K, R, S, pad_h, pad_w, g, BN)) return -1;
     splits = g.max_splits;
   } else {
     WgradGeom g;
-    if (plan_wgrad(N, H, W, C, K, R, S, pad_h, pad_w, g, BN)) return -1;
+    if (plan_wgrad(N, H, W, C, K, R, S, pad_h, pad_w, stride_h, stride_w, g, BN, Ho_given,
+                   Wo_given))
+      return -1;
     splits = g.splits;
   }
   if (splits <= 1) return 0;
   return static_cast<long long>(splits) * K * R * S * C * 4;
 }
 
-extern "C" int tgb_conv2d_wgrad_tf32(const float* dy, const float* x, float* dw, float* scratch,
-                                     long long scratch_bytes, int N, int H, int W, int C, int K,
-                                     int R, int S, int pad_h, int pad_w, int accumulate,
-                                     cudaStream_t stream) {
+static int run_wgrad(const WgradProblem& p, cudaStream_t stream) {
+  const int N = p.N, H = p.H, W = p.W, C = p.C, K = p.K, R = p.R, S = p.S;
   if (C % 4 != 0 || K % 4 != 0)
     return set_error("conv_wgrad: need C %% 4 == 0 and K %% 4 == 0");
-  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) |
-       reinterpret_cast<uintptr_t>(dw) | reinterpret_cast<uintptr_t>(scratch)) & 15)
+  if ((reinterpret_cast<uintptr_t>(p.x) | reinterpret_cast<uintptr_t>(p.dy) |
+       reinterpret_cast<uintptr_t>(p.dw) | reinterpret_cast<uintptr_t>(p.scratch)) & 15)
     return set_error("conv_wgrad: tensors must be 16-byte aligned");
-  const int Ho = H + 2 * pad_h - R + 1, Wo = W + 2 * pad_w - S + 1;
+  if ((p.x_sw | p.x_sh | p.x_sn | p.dy_sw) & 3)
+    return set_error("conv_wgrad: strides must be multiples of 4 elements (16 bytes)");
+  if (p.stride_h < 1 || p.stride_w < 1) return set_error("conv_wgrad: strides must be positive");
+  const int Ho = p.Ho > 0 ? p.Ho : (H + 2 * p.pad_h - R) / p.stride_h + 1;
+  const int Wo = p.Wo > 0 ? p.Wo : (W + 2 * p.pad_w - S) / p.stride_w + 1;
   if (Ho <= 0 || Wo <= 0) return set_error("conv_wgrad: empty output");
-  const bool fused = choose_wgrad_kernel(N, Ho, Wo, C, S) != 0;
+  const bool fused = wgrad_is_plain(p) && p.Ho <= 0 && p.Wo <= 0 &&
+                     choose_wgrad_kernel(N, Ho, Wo, C, S) != 0;
   WgradGeom g;
   WgradFusedGeom gf;
   int BN, splits;
   if (fused) {
-    if (plan_wgrad_fused(N, H, W, C, K, R, S, pad_h, pad_w, gf, BN)) return 1;
+    if (plan_wgrad_fused(N, H, W, C, K, R, S, p.pad_h, p.pad_w, gf, BN)) return 1;
     splits = gf.max_splits;
   } else {
-    if (plan_wgrad(N, H, W, C, K, R, S, pad_h, pad_w, g, BN)) return 1;
+    if (plan_wgrad(N, H, W, C, K, R, S, p.pad_h, p.pad_w, p.stride_h, p.stride_w, g, BN, p.Ho,
+                   p.Wo))
+      return 1;
     splits = g.splits;
   }
   const size_t dw_elems = static_cast<size_t>(K) * R * S * C;
-  const bool direct = splits <= 1 && !accumulate;
+  const bool direct = splits <= 1 && !p.accumulate;
   if (!direct) {
     const long long need = static_cast<long long>(splits) * dw_elems * 4;
-    if (scratch == nullptr || scratch_bytes < need)
+    if (p.scratch == nullptr || p.scratch_bytes < need)
       return set_error("conv_wgrad: scratch too small (need %lld bytes, got %lld)", need,
-                       scratch_bytes);
+                       p.scratch_bytes);
   }
-  float* out = direct ? dw : scratch;
+  float* out = direct ? p.dw : p.scratch;
   const int sms = sm_count();
   int rc;
   if (fused) {
-    rc = run_wgrad_fused(dy, x, out, gf, BN, stream);
+    rc = run_wgrad_fused(p.dy, p.x, out, gf, BN, stream);
   } else {
-    CUtensorMap mdy, mx;
+    CUtensorMap mdy, mx[4];
     {
       uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)N};
-      uint64_t strides[3] = {(uint64_t)K * 4, (uint64_t)g.Wo * K * 4,
-                             (uint64_t)g.Ho * g.Wo * K * 4};
+      uint64_t strides[3] = {(uint64_t)p.dy_sw * 4, (uint64_t)g.Wo * p.dy_sw * 4,
+                             (uint64_t)g.Ho * g.Wo * p.dy_sw * 4};
       uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
-      if (make_tensor_map(&mdy, dy, 4, 4, dims, strides, box, wgrad_tma_swizzle()))
+      if (make_tensor_map(&mdy, p.dy, 4, 4, dims, strides, box, wgrad_tma_swizzle()))
         return set_error("conv_wgrad: tensor map for dY failed");
     }
-    {
-      uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
-      uint64_t strides[3] = {(uint64_t)C * 4, (uint64_t)W * C * 4, (uint64_t)H * W * C * 4};
+    const int views = p.stride_h * p.stride_w;
+    for (int v = 0; v < 4; ++v) {
+      const int ph = v < views ? v / p.stride_w : 0, pw = v < views ? v % p.stride_w : 0;
+      const long long Hv = (H - ph + p.stride_h - 1) / p.stride_h;
+      const long long Wv = (W - pw + p.stride_w - 1) / p.stride_w;
+      if (Hv <= 0 || Wv <= 0) {
+        mx[v] = mx[0];
+        continue;
+      }
+      uint64_t dims[4] = {(uint64_t)C, (uint64_t)Wv, (uint64_t)Hv, (uint64_t)N};
+      uint64_t strides[3] = {(uint64_t)(p.x_sw * p.stride_w) * 4,
+                             (uint64_t)(p.x_sh * p.stride_h) * 4, (uint64_t)p.x_sn * 4};
       uint32_t box[4] = {32, (uint32_t)g.BW, (uint32_t)g.BH, (uint32_t)g.BNB};
-      if (make_tensor_map(&mx, x, 4, 4, dims, strides, box, wgrad_tma_swizzle()))
-        return set_error("conv_wgrad: tensor map for X failed");
+      if (make_tensor_map(&mx[v], p.x + ph * p.x_sh + pw * p.x_sw, 4, 4, dims, strides, box,
+                          wgrad_tma_swizzle()))
+        return set_error("conv_wgrad: tensor map for X (view %d) failed", v);
     }
     const int items = g.k_tiles * g.c_tiles * R * S * g.splits;
     const int grid = items < sms ? items : sms;
@@ -489,13 +556,74 @@ extern "C" int tgb_conv2d_wgrad_tf32(const float* dy, const float* x, float* dw,
     } else {
       for (int t = 0; t < R * S; ++t) ts.n[t] = splits;
     }
-    wgrad_reduce_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(scratch, dw, n4, ts, R * S,
-                                                                      C / 4, n4, accumulate);
+    wgrad_reduce_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(
+        p.scratch, p.dw, n4, ts, R * S, C / 4, n4, p.accumulate);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("wgrad_reduce launch: %s", cudaGetErrorString(e));
     count_launch();
   }
   return 0;
+}
+
+}  // namespace tgb
+
+extern "C" long long tgb_conv2d_wgrad_scratch_bytes(int N, int H, int W, int C, int K, int R,
+                                                    int S, int pad_h, int pad_w) {
+  return wgrad_scratch_need(N, H, W, C, K, R, S, pad_h, pad_w, 1, 1, true);
+}
+
+extern "C" long long tgb_conv2d_wgrad_strided_scratch_bytes(int N, int H, int W, int C, int K,
+                                                            int R, int S, int pad_h, int pad_w,
+                                                            int stride_h, int stride_w,
+                                                            int Ho, int Wo,
+                                                            long long dy_pixel_stride) {
+  const bool plain = stride_h == 1 && stride_w == 1 &&
+                     (dy_pixel_stride <= 0 || dy_pixel_stride == K);
+  return wgrad_scratch_need(N, H, W, C, K, R, S, pad_h, pad_w, stride_h, stride_w, plain, Ho,
+                            Wo);
+}
+
+extern "C" int tgb_conv2d_wgrad_tf32(const float* dy, const float* x, float* dw, float* scratch,
+                                     long long scratch_bytes, int N, int H, int W, int C, int K,
+                                     int R, int S, int pad_h, int pad_w, int accumulate,
+                                     cudaStream_t stream) {
+  WgradProblem p{dy, x, dw, scratch, scratch_bytes, N, H, W, C, K, R, S, pad_h, pad_w, 1, 1,
+                 C, static_cast<long long>(W) * C, static_cast<long long>(H) * W * C, K,
+                 accumulate};
+  return run_wgrad(p, stream);
+}
+
+extern "C" int tgb_conv2d_wgrad_strided_tf32(const float* dy, const float* x, float* dw,
+                                             float* scratch, long long scratch_bytes, int N,
+                                             int H, int W, int C, int K, int R, int S, int pad_h,
+                                             int pad_w, int stride_h, int stride_w, int Ho,
+                                             int Wo, long long dy_pixel_stride, int accumulate,
+                                             cudaStream_t stream) {
+  WgradProblem p{dy, x, dw, scratch, scratch_bytes, N, H, W, C, K, R, S, pad_h, pad_w, stride_h,
+                 stride_w, C, static_cast<long long>(W) * C, static_cast<long long>(H) * W * C,
+                 dy_pixel_stride > 0 ? dy_pixel_stride : K, accumulate};
+  p.Ho = Ho;
+  p.Wo = Wo;
+  return run_wgrad(p, stream);
+}
+
+// Weight gradient of the packed small-channel stem (conv_small.cu): dwv [K][R][32] with
+// dwv[k][r][4*s+c] = dW[k][c][r][s]; columns of taps / channels that do not exist receive the
+// correlation with whatever pixels the window covers there - the caller ignores them.
+extern "C" long long tgb_conv2d_stem_wgrad_scratch_bytes(int N, int Hp, int Wp, int K, int R,
+                                                         int stride_h, int stride_w) {
+  return wgrad_scratch_need(N, Hp, Wp - 7, 32, K, R, 1, 0, 0, stride_h, stride_w, false);
+}
+
+extern "C" int tgb_conv2d_stem_wgrad_tf32(const float* dy, const float* xp, float* dwv,
+                                          float* scratch, long long scratch_bytes, int N, int Hp,
+                                          int Wp, int K, int R, int stride_h, int stride_w,
+                                          cudaStream_t stream) {
+  if (Wp < 8) return set_error("stem_wgrad: packed rows must hold at least one 8-pixel window");
+  WgradProblem p{dy, xp, dwv, scratch, scratch_bytes, N, Hp, Wp - 7, 32, K, R, 1, 0, 0, stride_h,
+                 stride_w, 4, static_cast<long long>(Wp) * 4,
+                 static_cast<long long>(Hp) * Wp * 4, K, 0};
+  return run_wgrad(p, stream);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -37,6 +37,14 @@ inline int make_tensor_map(CUtensorMap* map, const void* base, int elem_bytes, i
                            const uint32_t* box, int swizzle_mode) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (fn == nullptr) return -1;
+  // cuTensorMapEncodeTiled is a driver call and wants a current context. A thread that has
+  // only been handed work (an autograd worker, an executor thread) may not have touched the
+  // runtime yet: bind the current device's primary context once per thread.
+  static thread_local bool context_bound = false;
+  if (!context_bound) {
+    cudaFree(nullptr);
+    context_bound = true;
+  }
   cuuint64_t gdims[5];
   cuuint64_t gstrides[5];
   cuuint32_t gbox[5];
@@ -55,6 +63,15 @@ inline int make_tensor_map(CUtensorMap* map, const void* base, int elem_bytes, i
                   : swizzle_mode == 2 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
                                       : CU_TENSOR_MAP_SWIZZLE_NONE,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r == CUDA_ERROR_INVALID_CONTEXT) {       // the thread switched devices since: bind again
+    cudaFree(nullptr);
+    r = fn(map, dt, static_cast<cuuint32_t>(rank), const_cast<void*>(base), gdims, gstrides, gbox,
+           estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+           swizzle_mode == 1   ? CU_TENSOR_MAP_SWIZZLE_128B
+           : swizzle_mode == 2 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                               : CU_TENSOR_MAP_SWIZZLE_NONE,
+           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
   if (r != CUDA_SUCCESS) {
     fprintf(stderr, "cuTensorMapEncodeTiled failed: %d (rank %d)\n", static_cast<int>(r), rank);
     return static_cast<int>(r);

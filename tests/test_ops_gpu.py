@@ -67,6 +67,168 @@ def test_conv2d_forward_backward_vs_fp32(case):
     assert rel_err(dw, rdw) < 2e-3
 
 
+# Shapes that reach the kernel variants the benchmark actually runs (the small cases above all
+# land in the plain <32/64/128, 0, 0> kernels): haloed tiles (needs >= 4 x 148 tiles of 8 x 16
+# pixels), resident filter bank, BN=256 with band tiles, forced split-K with the TMA reduce-add
+# epilogue, and the tap-fused weight gradient with 128-wide tiles.
+BIG_CONV_CASES = [
+    # N, C, H, W, K, env
+    (8, 64, 96, 96, 64, {}),                              # halo + resident weights, fused wgrad<64>
+    (8, 64, 96, 96, 64, {'TGB_FPROP_RESW': '0'}),          # halo, streamed weights
+    (8, 64, 96, 96, 64, {'TGB_FPROP_HALO': '0'}),          # same layer on the per-tap kernel
+    (4, 128, 96, 96, 32, {}),                             # halo<32>, fused wgrad<128>
+    (4, 32, 64, 64, 32, {'TGB_FPROP_HALO': '2'}),          # halo forced on a small grid
+    (5, 1024, 12, 12, 1024, {}),                          # BN=256, band tiles (12x2 x 5 images)
+    (5, 1024, 12, 12, 1024, {'TGB_FPROP_SPLITS': '3'}),    # split-K + TMA reduce-add
+    (16, 256, 24, 24, 512, {}),                           # micro-batch 16 shape of the 8-GPU run
+    (2, 2048, 6, 6, 2048, {}),                            # whole small images per tile
+]
+
+
+@pytest.mark.parametrize('case', BIG_CONV_CASES)
+def test_conv2d_benchmark_variants_vs_fp32(case, monkeypatch):
+    from torchgpipe_b200.ops import functional as TF
+    N, C, H, W, K, env = case
+    for key, value in env.items():
+        monkeypatch.setenv(key, value)
+    torch.manual_seed(11)
+    x = torch.randn(N, C, H, W, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    w = (torch.randn(K, C, 3, 3, device='cuda') / (C * 9) ** 0.5).contiguous(
+        memory_format=CL).requires_grad_()
+    for mode in (0, 1, 2):
+        y, stats = TF.conv2d(x, w, (1, 1), stats_mode=mode)
+        ref = F.conv2d(x, w, padding=1)
+        assert rel_err(y, ref) < 2e-3
+        if mode:
+            dims = (2, 3) if mode == 1 else (0, 2, 3)
+            yd = y.detach().double()
+            assert rel_err(stats[..., 0].double(), yd.sum(dims)) < 1e-3 or \
+                torch.allclose(stats[..., 0].double(), yd.sum(dims), atol=0.5)
+            assert rel_err(stats[..., 1].double(), (yd * yd).sum(dims)) < 1e-4
+    g = torch.randn_like(ref)
+    dx, dw = torch.autograd.grad(y, (x, w), g)
+    rdx, rdw = torch.autograd.grad(ref, (x, w), g)
+    assert rel_err(dx, rdx) < 2e-3
+    assert rel_err(dw, rdw) < 2e-3
+
+
+STRIDED_CASES = [
+    # N, C, H, W, K, (R, S), (sh, sw), (ph, pw) - every strided shape of the benchmark models:
+    # resnet/__init__.py:41 (1x1/2 downsample), bottleneck.py:22,28 (3x3/2), amoebanet
+    # __init__.py:28 / operations.py:71-84 (1x7, 7x1, 3x3, 1x1 with stride), operations.py:31-32
+    (2, 64, 16, 16, 64, (3, 3), (2, 2), (1, 1)),
+    (3, 32, 15, 17, 64, (3, 3), (2, 2), (1, 1)),          # odd extents: unequal parity classes
+    (2, 256, 14, 14, 512, (1, 1), (2, 2), (0, 0)),
+    (2, 64, 15, 15, 128, (1, 1), (2, 2), (0, 0)),
+    (2, 32, 12, 24, 32, (1, 7), (1, 2), (0, 3)),
+    (2, 32, 24, 12, 32, (7, 1), (2, 1), (3, 0)),
+    (2, 16, 20, 20, 32, (7, 7), (2, 2), (3, 3)),
+    (4, 128, 28, 28, 128, (3, 3), (2, 2), (1, 1)),
+    (2, 64, 9, 9, 64, (3, 3), (2, 2), (0, 0)),            # no padding
+    (2, 36, 16, 16, 40, (3, 3), (2, 2), (1, 1)),          # partial channel tiles
+]
+
+
+@pytest.mark.parametrize('case', STRIDED_CASES)
+def test_strided_conv2d_forward_backward_vs_fp32(case):
+    from torchgpipe_b200.ops import functional as TF
+    N, C, H, W, K, (R, S), stride, pad = case
+    torch.manual_seed(5)
+    x = torch.randn(N, C, H, W, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    w = (torch.randn(K, C, R, S, device='cuda') / (C * R * S) ** 0.5).contiguous(
+        memory_format=CL).requires_grad_()
+    y, stats = TF.conv2d(x, w, pad, stats_mode=2, stride=stride)
+    ref = F.conv2d(x, w, stride=stride, padding=pad)
+    assert y.shape == ref.shape and y.is_contiguous(memory_format=CL)
+    assert rel_err(y, ref) < 2e-3
+    assert rel_err(stats[:, 1], (ref * ref).sum((0, 2, 3))) < 2e-3
+    g = torch.randn_like(ref)
+    dx, dw = torch.autograd.grad(y, (x, w), g)
+    rdx, rdw = torch.autograd.grad(ref, (x, w), g)
+    assert rel_err(dx, rdx) < 2e-3
+    assert rel_err(dw, rdw) < 2e-3
+
+
+@pytest.mark.parametrize('hw', [14, 15])
+def test_factorized_reduce_convs_write_channel_halves_in_place(hw):
+    """The two halves of AmoebaNet's FactorizedReduce (reference operations.py:24-40): conv1 on
+    the even pixels, conv2 on the odd ones (shift by one, zero-pad the far edge = a 1x1 stride-2
+    convolution with padding -1), both written straight into their half of one output."""
+    from torchgpipe_b200.ops import functional as TF
+    torch.manual_seed(6)
+    N, C, H, W, K = 3, 64, hw, hw, 96
+    x = torch.randn(N, C, H, W, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    w1 = (torch.randn(K // 2, C, 1, 1, device='cuda') / 8).contiguous(memory_format=CL)
+    w2 = (torch.randn(K // 2, C, 1, 1, device='cuda') / 8).contiguous(memory_format=CL)
+    w1.requires_grad_(), w2.requires_grad_()
+    out, stats = TF.factorized_reduce_conv(x, w1, w2, {}, {})
+    shifted = F.pad(x[:, :, 1:, 1:], (0, 1, 0, 1))
+    ref = torch.cat([F.conv2d(x, w1, stride=2), F.conv2d(shifted, w2, stride=2)], dim=1)
+    assert out.shape == ref.shape and rel_err(out, ref) < 2e-3
+    assert rel_err(stats[:, 1], (ref * ref).sum((0, 2, 3))) < 2e-3
+    g = torch.randn_like(ref)
+    got = torch.autograd.grad(out, (x, w1, w2), g)
+    want = torch.autograd.grad(ref, (x, w1, w2), g)
+    for a, b in zip(got, want):
+        assert rel_err(a, b) < 2e-3
+
+
+STEM_CASES = [
+    # N, C, H, W, K, (R, S), stride, pad, channels_last input
+    (2, 3, 64, 64, 64, (7, 7), (2, 2), (3, 3), False),     # resnet/__init__.py:55
+    (2, 3, 56, 40, 64, (3, 3), (2, 2), (1, 1), False),     # amoebanet/__init__.py:54
+    (2, 3, 48, 48, 64, (3, 3), (1, 1), (1, 1), True),      # unet/__init__.py:44, first cell
+    (3, 1, 33, 31, 32, (5, 5), (1, 1), (2, 2), False),
+    (2, 4, 30, 30, 32, (3, 8), (2, 1), (1, 0), True),
+]
+
+
+@pytest.mark.parametrize('case', STEM_CASES)
+def test_small_channel_stem_vs_fp32(case):
+    from torchgpipe_b200.ops import functional as TF
+    N, C, H, W, K, (R, S), stride, pad, cl = case
+    torch.manual_seed(8)
+    x = torch.randn(N, C, H, W, device='cuda')
+    if cl:
+        x = x.contiguous(memory_format=CL)
+    w = (torch.randn(K, C, R, S, device='cuda') / (C * R * S) ** 0.5).requires_grad_()
+    cache = {}
+    y, stats = TF.stem_conv2d(x, w, pad, stride, stats_mode=1, cache=cache)
+    ref = F.conv2d(x, w, stride=stride, padding=pad)
+    assert y.shape == ref.shape
+    assert rel_err(y, ref) < 2e-3
+    assert rel_err(stats[..., 0], ref.sum((2, 3))) < 5e-3 or \
+        torch.allclose(stats[..., 0], ref.sum((2, 3)), atol=0.05)
+    g = torch.randn_like(ref)
+    dw, = torch.autograd.grad(y, w, g)
+    rdw, = torch.autograd.grad(ref, w, g)
+    assert rel_err(dw, rdw) < 2e-3
+    # cached packed weights follow an in-place parameter update
+    with torch.no_grad():
+        w.mul_(0.5)
+    TF.refresh_stem_weight(w, cache)
+    y2, _ = TF.stem_conv2d(x, w, pad, stride, cache=cache)
+    assert rel_err(y2, 0.5 * ref) < 2e-3
+
+
+@pytest.mark.parametrize('C,K,bias', [(64, 1, True), (32, 2, False), (256, 4, True), (8, 3, True)])
+def test_narrow_head_conv_vs_fp32(C, K, bias):
+    from torchgpipe_b200.ops import functional as TF
+    torch.manual_seed(9)
+    x = torch.randn(3, C, 19, 23, device='cuda').contiguous(memory_format=CL).requires_grad_()
+    w = (torch.randn(K, C, 1, 1, device='cuda') / C ** 0.5).requires_grad_()
+    b = torch.randn(K, device='cuda').requires_grad_() if bias else None
+    y = TF.head_conv2d(x, w, b)
+    ref = F.conv2d(x, w, b)
+    assert torch.allclose(y, ref, rtol=1e-4, atol=1e-5)      # plain fp32 arithmetic
+    g = torch.randn_like(ref)
+    ins = (x, w) + ((b,) if bias else ())
+    got = torch.autograd.grad(y, ins, g)
+    want = torch.autograd.grad(ref, ins, g)
+    for a, r in zip(got, want):
+        assert rel_err(a, r) < 1e-4
+
+
 @pytest.mark.parametrize('mode', [1, 2])
 def test_conv_epilogue_statistics(mode):
     from torchgpipe_b200.ops import functional as TF
@@ -135,38 +297,61 @@ def test_fused_unet_cell_matches_unfused_in_eval_and_train_without_dropout():
     assert rel_err(fused.weight.grad, ref[0].weight.grad) < 2e-2
 
 
-def test_stem_with_three_input_channels_uses_library_conv_but_fused_norm():
+def test_stem_with_three_input_channels_runs_on_the_packed_window_path():
+    from torchgpipe_b200 import ops
     from torchgpipe_b200.ops.modules import ConvInstNormLeaky
     torch.manual_seed(5)
     conv = nn.Conv2d(3, 64, 3, padding=1, bias=False).cuda()
     ref = nn.Sequential(copy.deepcopy(conv), nn.InstanceNorm2d(64), nn.LeakyReLU(0.01)).cuda()
     fused = ConvInstNormLeaky(conv, 0.0, 1e-5, 0.01).cuda()
     x = torch.rand(2, 3, 32, 32, device='cuda')
-    assert rel_err(fused(x), ref(x)) < 1e-4
+    before = ops.launch_count()
+    assert rel_err(fused(x), ref(x)) < 3e-3
+    assert ops.launch_count() - before >= 4      # pack, conv, prepare, normalise: no library conv
+
+
+def _tf32_bound_check(fused, plain, x, slack=3.0, floor=2e-3):
+    """Compares ``fused`` with a float64 oracle of ``plain``. Stated bound: the fused model may be
+    at most ``slack`` times as far from the oracle as the same plain model run by PyTorch with
+    TF32 convolutions (the reference's arithmetic), plus ``floor``. That measures the kernels'
+    rounding against the rounding the reference itself has, however ill-conditioned the net."""
+    oracle = copy.deepcopy(plain).double()
+    xd = x.double()
+    ref = oracle(xd)
+    ref.mean().backward()
+    torch.backends.cudnn.allow_tf32 = True
+    torch.backends.cuda.matmul.allow_tf32 = True
+    base = plain(x)
+    base.mean().backward()
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    out = fused(x)
+    out.mean().backward()
+    assert rel_err(out.double(), ref) <= slack * rel_err(base.double(), ref) + floor
+    worst = 0.0
+    for (n, p), (_, q), (_, o) in zip(fused.named_parameters(), plain.named_parameters(),
+                                      oracle.named_parameters()):
+        if o.grad is None:
+            continue
+        e_fused, e_base = rel_err(p.grad.double(), o.grad), rel_err(q.grad.double(), o.grad)
+        assert e_fused <= slack * e_base + floor, (n, e_fused, e_base)
+        worst = max(worst, e_fused)
+    return worst
 
 
 def test_converted_unet_matches_plain_unet():
     from torchgpipe_b200 import ops
     from torchgpipe_b200.models import unet
     torch.manual_seed(6)
+    # eval mode: no dropout; InstanceNorm uses batch statistics in both modes
     plain = unet(depth=2, num_convs=2, base_channels=32).cuda().eval()
     fused = ops.convert_to_sm100(copy.deepcopy(plain)).cuda().eval()
     assert len(fused) == len(plain)
     assert list(fused.state_dict().keys()) == list(plain.state_dict().keys())
     x = torch.rand(2, 3, 32, 32, device='cuda')
     before = ops.launch_count()
-    out, ref = fused(x), plain(x)
+    _tf32_bound_check(fused, plain, x)
     assert ops.launch_count() > before
-    assert rel_err(out, ref) < 1e-2
-
-    # training step (dropout off via p=0 is not possible here: compare grads in eval mode,
-    # InstanceNorm uses batch statistics in both modes)
-    out.mean().backward()
-    ref.mean().backward()
-    # deep stack of norm layers: TF32 rounding is amplified layer by layer, so compare direction
-    for (n, p), (_, q) in zip(fused.named_parameters(), plain.named_parameters()):
-        cos = F.cosine_similarity(p.grad.flatten(), q.grad.flatten(), dim=0).item()
-        assert cos > 0.98, (n, cos)
 
 
 def test_dropout_mask_is_reproduced_under_checkpointing():
@@ -249,7 +434,7 @@ def test_cuda_graph_stage_matches_eager_stage():
     # 3 steps x 3 micro-batches: the last micro-batch of every step skips its recomputation
     assert sum(st.recomputes_skipped for st in pipe._graphed.values()) == 3
     for step, ((le, ge), (lg, gg)) in enumerate(zip(eager, graphed)):
-        assert rel_err(lg, le) < 5e-3           # same loss trajectory over optimiser steps
+        assert rel_err(lg, le) < 1e-2           # same loss trajectory over optimiser steps
         if step == 0:                           # later steps: TF32 noise makes weights diverge
             for a, b in zip(gg, ge):
                 assert F.cosine_similarity(a.flatten(), b.flatten(), dim=0).item() > 0.995
@@ -367,13 +552,58 @@ def test_converted_small_resnet_matches_plain():
     fused = ops.convert_to_sm100(copy.deepcopy(plain))
     assert len(fused) == len(plain)
     x = torch.randn(4, 3, 64, 64, device='cuda')
-    out, ref = fused(x), plain(x)
-    assert rel_err(out, ref) < 2e-2
-    out.square().mean().backward()
-    ref.square().mean().backward()
-    for (n, p), (_, q) in zip(fused.named_parameters(), plain.named_parameters()):
-        cos = F.cosine_similarity(p.grad.flatten(), q.grad.flatten(), dim=0).item()
-        assert cos > 0.97, (n, cos)
+    _tf32_bound_check(fused, plain, x, slack=4.0, floor=5e-3)
+
+
+def test_converted_small_amoebanet_matches_plain():
+    from torchgpipe_b200 import ops
+    from torchgpipe_b200.models import amoebanetd
+    torch.manual_seed(25)
+    plain = amoebanetd(num_classes=10, num_layers=3, num_filters=64).cuda()
+    fused = ops.convert_to_sm100(copy.deepcopy(plain))
+    assert list(fused.state_dict().keys()) == list(plain.state_dict().keys())
+    x = torch.randn(4, 3, 224, 224, device='cuda')
+    _tf32_bound_check(fused, plain, x, slack=4.0, floor=5e-3)
+
+
+def _kernel_names(fn):
+    from torch.profiler import ProfilerActivity, profile
+    fn()                                    # warm-up: lazy initialisation launches
+    torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        fn()
+        torch.cuda.synchronize()
+    return [e.key for e in prof.key_averages()]
+
+
+@pytest.mark.parametrize('which', ['unet', 'resnet', 'amoebanet'])
+def test_converted_models_launch_no_library_convolution(which):
+    """Stems, strided layers and the 1-channel head included: a training step of a converted
+    benchmark model contains no cuDNN / cuBLAS convolution or GEMM kernel."""
+    from torchgpipe_b200 import ops
+    from torchgpipe_b200.models import amoebanetd, unet
+    from torchgpipe_b200.models.resnet import build_resnet
+    torch.manual_seed(26)
+    if which == 'unet':
+        model, hw = unet(depth=2, num_convs=2, base_channels=32), 64
+    elif which == 'resnet':
+        model, hw = build_resnet([1, 1, 1, 1], num_classes=12), 64
+    else:
+        model, hw = amoebanetd(num_classes=12, num_layers=3, num_filters=64), 224
+    model = ops.convert_to_sm100(model).cuda()
+    x = torch.randn(4, 3, hw, hw, device='cuda')
+
+    def step():
+        model.zero_grad()
+        model(x).square().mean().backward()
+
+    names = _kernel_names(step)
+    library = [n for n in names if any(tag in n.lower() for tag in (
+        'cudnn', 'cutlass', 'xmma', 'implicit_convolve', 'wgrad', 'dgrad', 'gemm', 'cublas',
+        'winograd', 'conv2d_grouped', 'nchwtonhwc', 'nhwctonchw')) and 'tgb::' not in n
+        and not n.startswith('tgb') and 'dgrad_weight' not in n]
+    assert not library, library
+    assert any('conv_fprop_tf32_kernel' in n for n in names)
 
 
 @pytest.mark.multigpu

@@ -11,7 +11,8 @@ from typing import List, Tuple
 
 from torch import nn
 
-from torchgpipe_b200.ops.modules import (Absorbed, AbsorbedBatchNorm2d, BatchNormResidualAct,
+from torchgpipe_b200.ops.modules import (Absorbed, AbsorbedBatchNorm2d, AmoebaFactorizedReduce,
+                                         AmoebaStem, BatchNormResidualAct,
                                          Conv2dTC, ConvBatchNormAct, ConvInstNormLeaky,
                                          GlobalAvgPoolNHWC, LinearTC, MaxPool2x2, Pool2dNHWC,
                                          UpsamplePopCat)
@@ -20,8 +21,12 @@ __all__ = ['convert_to_sm100']
 
 
 def _plain_conv(m: nn.Module) -> bool:
-    return (isinstance(m, nn.Conv2d) and m.stride == (1, 1) and m.dilation == (1, 1)
-            and m.groups == 1 and m.padding_mode == 'zeros' and not isinstance(m.padding, str))
+    """A convolution some native path covers (implicit GEMM, packed stem or streaming head)."""
+    from torchgpipe_b200.ops import functional as TF
+    return (isinstance(m, nn.Conv2d) and m.padding_mode == 'zeros'
+            and not isinstance(m.padding, str)
+            and TF.conv_kind(m.in_channels, m.out_channels, m.kernel_size, m.stride,
+                             m.dilation, m.groups) is not None)
 
 
 def _match_unet_cell(layers: List[Tuple[str, nn.Module]], i: int) -> bool:
@@ -105,6 +110,29 @@ def _convert_pool(m: nn.Module):
     return None
 
 
+def _children(m: nn.Module) -> List[str]:
+    return [name for name, _ in m.named_children()]
+
+
+def _is_amoeba_stem(m: nn.Module) -> bool:
+    """``relu -> conv -> bn`` module of AmoebaNet (reference amoebanet/__init__.py:47-58)."""
+    return (type(m).__name__ == 'Stem' and _children(m) == ['relu', 'conv', 'bn']
+            and type(m.relu) is nn.ReLU and type(m.conv) is nn.Conv2d and m.conv.bias is None
+            and type(m.bn) is nn.BatchNorm2d and _plain_conv(m.conv))
+
+
+def _is_factorized_reduce(m: nn.Module) -> bool:
+    """AmoebaNet's stride-2 reduction (reference amoebanet/operations.py:24-40)."""
+    if type(m).__name__ != 'FactorizedReduce' or \
+            _children(m) != ['relu', 'pad', 'conv1', 'conv2', 'bn']:
+        return False
+    convs_ok = all(type(c) is nn.Conv2d and c.kernel_size == (1, 1) and c.stride == (2, 2)
+                   and c.padding == (0, 0) and c.bias is None and c.groups == 1
+                   for c in (m.conv1, m.conv2))
+    return (convs_ok and type(m.bn) is nn.BatchNorm2d and type(m.pad) is nn.ZeroPad2d
+            and tuple(m.pad.padding) == (0, 1, 0, 1))
+
+
 def _fused_residual(residual: nn.Module, bn, relu: bool) -> nn.Module:
     downsample = residual.module.downsample
     if downsample is not None:
@@ -183,10 +211,16 @@ def _convert_any(module: nn.Module) -> nn.Module:
         return module
     if type(module) is nn.Sequential:
         return _convert_sequential(module)
+    if isinstance(module, (AmoebaStem, AmoebaFactorizedReduce)):
+        return module
+    if _is_amoeba_stem(module):
+        return AmoebaStem(module)
+    if _is_factorized_reduce(module):
+        return AmoebaFactorizedReduce(module)
     pool = _convert_pool(module)
     if pool is not None:
         return pool
-    if _plain_conv(module) and module.in_channels % 4 == 0 and module.out_channels % 4 == 0:
+    if _plain_conv(module):
         return Conv2dTC(module)         # type: ignore[arg-type]
     if type(module) is nn.Linear and module.in_features % 4 == 0 \
             and module.out_features % 4 == 0:

@@ -13,7 +13,8 @@ from torch import Tensor
 
 from torchgpipe_b200.ops import _lib
 
-__all__ = ['linear', 'conv2d', 'conv2d_forward', 'instnorm_leaky', 'channel_moments', 'conv_supported',
+__all__ = ['linear', 'conv2d', 'conv2d_forward', 'conv2d_dgrad', 'conv_kind', 'stem_conv2d',
+           'head_conv2d', 'factorized_reduce_conv', 'refresh_stem_weight', 'add_channel_bias', 'instnorm_leaky', 'channel_moments', 'conv_supported',
            'refresh_dgrad_weight', 'batchnorm_act', 'maxpool2x2', 'upsample2x_cat', 'pool2d',
            'pool_supported', 'global_avgpool', 'add_act', 'batchnorm_add_act', 'conv2d_plan']
 
@@ -27,63 +28,127 @@ def _cl(t: Tensor) -> Tensor:
     return t if t.is_contiguous(memory_format=_CL) else t.contiguous(memory_format=_CL)
 
 
-def conv_supported(c_in: int, c_out: int, stride, dilation, groups: int) -> bool:
-    """Whether the tcgen05 kernels cover this convolution (else callers use ATen/cuDNN)."""
-    stride = tuple(stride) if not isinstance(stride, int) else (stride, stride)
-    dilation = tuple(dilation) if not isinstance(dilation, int) else (dilation, dilation)
-    return (stride == (1, 1) and dilation == (1, 1) and groups == 1
-            and c_in % 4 == 0 and c_out % 4 == 0)
+def _pair(v) -> Tuple[int, int]:
+    return (int(v), int(v)) if isinstance(v, int) else (int(v[0]), int(v[1]))
+
+
+def conv_kind(c_in: int, c_out: int, kernel_size, stride, dilation, groups: int) -> Optional[str]:
+    """Which native path covers a convolution: ``'tc'`` (implicit GEMM on tcgen05, strides up to
+    2x2), ``'stem'`` (1-4 input channels, filter rows of at most 8 taps: packed-window tcgen05
+    path), ``'head'`` (1x1, stride 1, at most 4 output channels: streaming dot product) or
+    ``None`` (not covered)."""
+    sh, sw = _pair(stride)
+    R, S = _pair(kernel_size)
+    if _pair(dilation) != (1, 1) or groups != 1 or sh < 1 or sw < 1 or sh * sw > 4:
+        return None
+    if c_in % 4 == 0 and c_out % 4 == 0:
+        return 'tc'
+    if c_in <= 4 and c_out % 4 == 0 and S <= 8:
+        return 'stem'
+    if c_in % 4 == 0 and c_out <= 4 and (R, S, sh, sw) == (1, 1, 1, 1):
+        return 'head'
+    return None
+
+
+def conv_supported(c_in: int, c_out: int, stride, dilation, groups: int,
+                   kernel_size=3) -> bool:
+    """Whether the tcgen05 implicit-GEMM kernels cover this convolution directly."""
+    return conv_kind(c_in, c_out, kernel_size, stride, dilation, groups) == 'tc'
+
+
+def _out_hw(H: int, W: int, R: int, S: int, padding, stride) -> Tuple[int, int]:
+    return ((H + 2 * padding[0] - R) // stride[0] + 1, (W + 2 * padding[1] - S) // stride[1] + 1)
 
 
 def conv2d_forward(x: Tensor, w: Tensor, padding: Tuple[int, int], stats_mode: int = 0,
+                   stride: Tuple[int, int] = (1, 1), out: Optional[Tensor] = None,
+                   out_hw: Optional[Tuple[int, int]] = None,
                    ) -> Tuple[Tensor, Optional[Tensor]]:
     """Raw forward: returns ``(y, stats)``; ``stats`` is ``[N,K,2]`` (mode 1), ``[K,2]`` (mode 2)
-    or ``None``. No autograd."""
+    or ``None``. No autograd. ``out``: write into this ``[N,K,Ho,Wo]`` tensor, which may be a
+    channel slice of a wider channels-last tensor (a concatenation written in place).
+    ``out_hw``: fix the output extent instead of deriving it (padding that differs between the
+    near and the far edge: the far edge is zero-filled as far as the extent asks)."""
     lib = _lib.require()
     x, w = _cl(x), _cl(w)
     N, C, H, W = x.shape
     K, Cw, R, S = w.shape
     assert C == Cw, f'channel mismatch: input {C}, weight {Cw}'
     ph, pw = padding
-    Ho, Wo = H + 2 * ph - R + 1, W + 2 * pw - S + 1
-    y = torch.empty((N, K, Ho, Wo), device=x.device, dtype=torch.float32, memory_format=_CL)
+    sh, sw = stride
+    Ho, Wo = out_hw if out_hw is not None else _out_hw(H, W, R, S, padding, stride)
+    if out is None:
+        y = torch.empty((N, K, Ho, Wo), device=x.device, dtype=torch.float32, memory_format=_CL)
+        y_pixel = K
+    else:
+        y = out
+        assert y.shape == (N, K, Ho, Wo) and _is_channel_slice(y), \
+            'out must be a channel slice of an NHWC tensor'
+        y_pixel = _pixel_stride(y)
     stats = None
     if stats_mode == 1:
         stats = torch.zeros((N, K, 2), device=x.device, dtype=torch.float32)
     elif stats_mode == 2:
         stats = torch.zeros((K, 2), device=x.device, dtype=torch.float32)
     with torch.cuda.device(x.device):
-        rc = lib.tgb_conv2d_fprop_tf32(_lib.ptr(x), _lib.ptr(w), _lib.ptr(y), _lib.ptr(stats),
-                                       _c_int(N), _c_int(H), _c_int(W), _c_int(C), _c_int(K),
-                                       _c_int(R), _c_int(S), _c_int(ph), _c_int(pw),
-                                       _c_int(stats_mode), _lib.stream_ptr(x.device))
+        if (sh, sw) == (1, 1) and y_pixel == K and out_hw is None:
+            rc = lib.tgb_conv2d_fprop_tf32(_lib.ptr(x), _lib.ptr(w), _lib.ptr(y), _lib.ptr(stats),
+                                           _c_int(N), _c_int(H), _c_int(W), _c_int(C), _c_int(K),
+                                           _c_int(R), _c_int(S), _c_int(ph), _c_int(pw),
+                                           _c_int(stats_mode), _lib.stream_ptr(x.device))
+        else:
+            rc = lib.tgb_conv2d_fprop_strided_tf32(
+                _lib.ptr(x), _lib.ptr(w), _lib.ptr(y), _lib.ptr(stats), _c_int(N), _c_int(H),
+                _c_int(W), _c_int(C), _c_int(K), _c_int(R), _c_int(S), _c_int(ph), _c_int(pw),
+                _c_int(sh), _c_int(sw), _c_int(Ho if out_hw else 0), _c_int(Wo if out_hw else 0),
+                _c_ll(y_pixel), _c_int(stats_mode), _lib.stream_ptr(x.device))
     _lib.check(rc, 'tgb_conv2d_fprop_tf32')
     return y, stats
 
 
-def _conv2d_wgrad(dy: Tensor, x: Tensor, w_shape, padding: Tuple[int, int]) -> Tensor:
+def _conv2d_wgrad(dy: Tensor, x: Tensor, w_shape, padding: Tuple[int, int],
+                  stride: Tuple[int, int] = (1, 1), fixed_hw: bool = False) -> Tensor:
+    """``dy`` may be a channel slice of a wider NHWC tensor (gradient of a concatenation)."""
     lib = _lib.require()
     lib.tgb_conv2d_wgrad_scratch_bytes.restype = _c_ll
+    lib.tgb_conv2d_wgrad_strided_scratch_bytes.restype = _c_ll
     N, C, H, W = x.shape
     K, _, R, S = w_shape
     ph, pw = padding
+    sh, sw = stride
+    dy_pixel = _pixel_stride(dy)
+    plain = (sh, sw) == (1, 1) and dy_pixel == K and not fixed_hw
+    ho, wo = (dy.size(2), dy.size(3)) if fixed_hw else (0, 0)
     args = (_c_int(N), _c_int(H), _c_int(W), _c_int(C), _c_int(K), _c_int(R), _c_int(S),
             _c_int(ph), _c_int(pw))
-    need = lib.tgb_conv2d_wgrad_scratch_bytes(*args)
+    if plain:
+        need = lib.tgb_conv2d_wgrad_scratch_bytes(*args)
+    else:
+        need = lib.tgb_conv2d_wgrad_strided_scratch_bytes(*args, _c_int(sh), _c_int(sw),
+                                                          _c_int(ho), _c_int(wo), _c_ll(dy_pixel))
     if need < 0:
         _lib.check(1, 'tgb_conv2d_wgrad_scratch_bytes')
     scratch = torch.empty(need // 4, device=x.device, dtype=torch.float32) if need else None
     dw = torch.empty(w_shape, device=x.device, dtype=torch.float32, memory_format=_CL)
     with torch.cuda.device(x.device):
-        rc = lib.tgb_conv2d_wgrad_tf32(_lib.ptr(dy), _lib.ptr(x), _lib.ptr(dw), _lib.ptr(scratch),
-                                       _c_ll(need), *args, _c_int(0),
-                                       _lib.stream_ptr(x.device))
+        if plain:
+            rc = lib.tgb_conv2d_wgrad_tf32(_lib.ptr(dy), _lib.ptr(x), _lib.ptr(dw),
+                                           _lib.ptr(scratch), _c_ll(need), *args, _c_int(0),
+                                           _lib.stream_ptr(x.device))
+        else:
+            rc = lib.tgb_conv2d_wgrad_strided_tf32(_lib.ptr(dy), _lib.ptr(x), _lib.ptr(dw),
+                                                   _lib.ptr(scratch), _c_ll(need), *args,
+                                                   _c_int(sh), _c_int(sw), _c_int(ho), _c_int(wo),
+                                                   _c_ll(dy_pixel), _c_int(0),
+                                                   _lib.stream_ptr(x.device))
     _lib.check(rc, 'tgb_conv2d_wgrad_tf32')
     return dw
 
 
-def _dgrad_weight(w: Tensor, cache: Optional[dict]) -> Tensor:
-    """Tap-flipped, channel-transposed weights (KRSC memory) for the data-gradient pass.
+def _dgrad_weight(w: Tensor, cache: Optional[dict], padding: Tuple[int, int] = (0, 0),
+                  stride: Tuple[int, int] = (1, 1)) -> Tensor:
+    """Weights of the data-gradient pass (KRSC memory): tap-flipped and channel-transposed; for a
+    strided convolution one such bank per input-pixel parity class, concatenated (flat buffer).
 
     ``cache`` is a dict owned by the calling module: with several micro-batches per optimiser
     step the transform then runs once per parameter version instead of once per backward call.
@@ -91,38 +156,132 @@ def _dgrad_weight(w: Tensor, cache: Optional[dict]) -> Tensor:
     if cache is not None:
         if cache.get('version') == w._version and cache.get('ptr') == w.data_ptr():
             return cache['wt']
+    lib = _lib.require()
     K, C, R, S = w.shape
     old = cache.get('wt') if cache is not None else None
-    if old is not None and old.shape == (C, K, R, S) and old.device == w.device:
-        wt = old                # keep the address: captured CUDA graphs read this buffer
-    else:
-        wt = torch.empty((C, K, R, S), device=w.device, dtype=torch.float32, memory_format=_CL)
     src = _cl(w.detach())
-    with torch.cuda.device(w.device):
-        rc = _lib.require().tgb_dgrad_weight(_lib.ptr(src), _lib.ptr(wt), _c_int(K), _c_int(C),
-                                             _c_int(R), _c_int(S), _lib.stream_ptr(w.device))
-    _lib.check(rc, 'tgb_dgrad_weight')
+    if stride == (1, 1):
+        if old is not None and old.shape == (C, K, R, S) and old.device == w.device:
+            wt = old                # keep the address: captured CUDA graphs read this buffer
+        else:
+            wt = torch.empty((C, K, R, S), device=w.device, dtype=torch.float32,
+                             memory_format=_CL)
+        with torch.cuda.device(w.device):
+            rc = lib.tgb_dgrad_weight(_lib.ptr(src), _lib.ptr(wt), _c_int(K), _c_int(C),
+                                      _c_int(R), _c_int(S), _lib.stream_ptr(w.device))
+        _lib.check(rc, 'tgb_dgrad_weight')
+    else:
+        lib.tgb_dgrad_weight_strided_elems.restype = _c_ll
+        geom = (_c_int(K), _c_int(C), _c_int(R), _c_int(S), _c_int(padding[0]),
+                _c_int(padding[1]), _c_int(stride[0]), _c_int(stride[1]))
+        elems = max(4, int(lib.tgb_dgrad_weight_strided_elems(*geom)))
+        if old is not None and old.dim() == 1 and old.numel() == elems \
+                and old.device == w.device:
+            wt = old
+        else:
+            wt = torch.empty(elems, device=w.device, dtype=torch.float32)
+        with torch.cuda.device(w.device):
+            rc = lib.tgb_dgrad_weight_strided(_lib.ptr(src), _lib.ptr(wt), *geom,
+                                              _lib.stream_ptr(w.device))
+        _lib.check(rc, 'tgb_dgrad_weight_strided')
     if cache is not None:
         cache['version'], cache['ptr'], cache['wt'] = w._version, w.data_ptr(), wt
+        cache['geom'] = (padding, stride)
     return wt
 
 
 def refresh_dgrad_weight(w: Tensor, cache: dict) -> None:
     """Brings a cached dgrad weight up to date in place (no-op if never built or current)."""
     if 'wt' in cache and (cache.get('version') != w._version or cache.get('ptr') != w.data_ptr()):
-        _dgrad_weight(w, cache)
+        padding, stride = cache.get('geom', ((0, 0), (1, 1)))
+        _dgrad_weight(w, cache, padding, stride)
+
+
+def refresh_stem_weight(w: Tensor, cache: dict) -> None:
+    """Brings a cached packed stem weight up to date in place (no-op if never built)."""
+    if 'stem_w' in cache and (cache.get('stem_version') != w._version
+                              or cache.get('stem_ptr') != w.data_ptr()):
+        cache['stem_w'].copy_(_stem_weight(w))
+        cache['stem_version'], cache['stem_ptr'] = w._version, w.data_ptr()
+
+
+def add_channel_bias(y: Tensor, bias: Tensor) -> Tensor:
+    """``y + bias[None, :, None, None]`` (one ATen broadcast add; convolution biases are rare in
+    the benchmark models - every conv is followed by a normalisation)."""
+    return y + bias.view(1, -1, 1, 1)
+
+
+def _pixel_stride(t: Tensor) -> int:
+    """Elements between consecutive pixels of an NHWC(-slice) tensor; strides of size-1
+    dimensions carry no information, so take the innermost dimension that has extent."""
+    N, K, H, W = t.shape
+    if W > 1:
+        return t.stride(3)
+    if H > 1:
+        return t.stride(2)
+    if N > 1:
+        return t.stride(0)
+    return K
+
+
+def _is_channel_slice(t: Tensor) -> bool:
+    """A ``[N,K,H,W]`` view whose pixels are K consecutive floats inside a wider (or equally
+    wide) NHWC tensor: pixel (n,h,w) starts ``((n*H + h)*W + w) * pixel_stride`` elements in."""
+    if t.dim() != 4 or (t.size(1) > 1 and t.stride(1) != 1) or t.data_ptr() % 16:
+        return False
+    N, K, H, W = t.shape
+    ps = _pixel_stride(t)
+    return (ps % 4 == 0 and ps >= K and (W == 1 or t.stride(3) == ps)
+            and (H == 1 or t.stride(2) == W * ps) and (N == 1 or t.stride(0) == H * W * ps))
+
+
+def conv2d_dgrad(dy: Tensor, w: Tensor, x_shape, padding: Tuple[int, int],
+                 stride: Tuple[int, int] = (1, 1), cache: Optional[dict] = None,
+                 out: Optional[Tensor] = None, keep_untouched: bool = False,
+                 fixed_hw: bool = False) -> Tensor:
+    """Data gradient of ``conv2d`` on the tcgen05 kernels (one stride-1 launch per input-pixel
+    parity class for a strided convolution). ``dy`` may be a channel slice of a wider NHWC
+    gradient. ``out`` / ``keep_untouched``: write into an existing dense dX and leave the pixels
+    this convolution never reads alone."""
+    K, C, R, S = w.shape
+    N, _, H, W = x_shape
+    ph, pw = padding
+    wt = _dgrad_weight(w, cache, padding, stride)
+    if stride == (1, 1) and out is None:
+        dx, _ = conv2d_forward(_cl(dy), wt, (R - 1 - ph, S - 1 - pw), 0)
+        return dx
+    if not _is_channel_slice(dy):
+        dy = _cl(dy)
+    dx = out if out is not None else torch.empty((N, C, H, W), device=dy.device,
+                                                 dtype=torch.float32, memory_format=_CL)
+    assert dx.is_contiguous(memory_format=_CL)
+    with torch.cuda.device(dy.device):
+        rc = _lib.require().tgb_conv2d_dgrad_tf32(
+            _lib.ptr(dy), _lib.ptr(wt), _lib.ptr(dx), _c_int(N), _c_int(H), _c_int(W), _c_int(C),
+            _c_int(K), _c_int(R), _c_int(S), _c_int(ph), _c_int(pw), _c_int(stride[0]),
+            _c_int(stride[1]), _c_int(dy.size(2) if fixed_hw else 0),
+            _c_int(dy.size(3) if fixed_hw else 0), _c_ll(_pixel_stride(dy)),
+            _c_int(int(keep_untouched)),
+            _lib.stream_ptr(dy.device))
+    _lib.check(rc, 'tgb_conv2d_dgrad_tf32')
+    return dx
+
+
+def _dense_nhwc(t: Tensor) -> bool:
+    return t.is_contiguous(memory_format=_CL)
 
 
 class _Conv2d(torch.autograd.Function):
-    """Stride-1 convolution; backward = dgrad (same tcgen05 kernel, flipped weights) + wgrad."""
+    """Convolution on tcgen05; backward = dgrad (same kernel, derived weights) + wgrad."""
 
     @staticmethod
     def forward(ctx, x: Tensor, w: Tensor, ph: int, pw: int, stats_mode: int,  # type: ignore[override]
-                cache: Optional[dict]):
+                cache: Optional[dict], sh: int = 1, sw: int = 1):
         x, w = _cl(x), _cl(w)
-        y, stats = conv2d_forward(x, w, (ph, pw), stats_mode)
+        y, stats = conv2d_forward(x, w, (ph, pw), stats_mode, (sh, sw))
         ctx.save_for_backward(x, w)
         ctx.padding = (ph, pw)
+        ctx.stride = (sh, sw)
         ctx.cache = cache
         if stats is None:
             stats = x.new_empty(0)
@@ -132,29 +291,243 @@ class _Conv2d(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy: Tensor, _dstats):  # type: ignore[override]
         x, w = ctx.saved_tensors
-        ph, pw = ctx.padding
-        K, C, R, S = w.shape
-        dy = _cl(dy)
+        # a channel slice of an NHWC gradient (this output was one part of a concatenation) is
+        # read in place; anything else is made dense NHWC
+        if not _is_channel_slice(dy):
+            dy = _cl(dy)
         dx = dw = None
-        if ctx.needs_input_grad[0]:
-            if conv_supported(K, C, 1, 1, 1):
-                # dX = conv(dY, W^T flipped), pad' = R-1-pad
-                dx, _ = conv2d_forward(dy, _dgrad_weight(w, ctx.cache), (R - 1 - ph, S - 1 - pw), 0)
-            else:
-                dx = torch.nn.grad.conv2d_input(x.shape, w, dy, padding=(ph, pw))
         if ctx.needs_input_grad[1]:
-            dw = _conv2d_wgrad(dy, x, w.shape, (ph, pw))
-        return dx, dw, None, None, None, None
+            dw = _conv2d_wgrad(dy, x, w.shape, ctx.padding, ctx.stride)
+        if ctx.needs_input_grad[0]:
+            dx = conv2d_dgrad(dy, w, x.shape, ctx.padding, ctx.stride, ctx.cache)
+        return dx, dw, None, None, None, None, None, None
 
 
 def conv2d(x: Tensor, w: Tensor, padding: Tuple[int, int], stats_mode: int = 0,
-           cache: Optional[dict] = None) -> Tuple[Tensor, Optional[Tensor]]:
-    """Differentiable stride-1 convolution on tcgen05. Returns ``(y, stats or None)``.
+           cache: Optional[dict] = None, stride: Tuple[int, int] = (1, 1),
+           ) -> Tuple[Tensor, Optional[Tensor]]:
+    """Differentiable convolution on tcgen05 (strides up to 2x2, any integer padding including
+    negative = crop). Returns ``(y, stats or None)``.
 
     ``cache``: optional dict owned by the caller, reused across calls to keep derived weights.
     """
-    y, stats = _Conv2d.apply(x, w, int(padding[0]), int(padding[1]), int(stats_mode), cache)
+    y, stats = _Conv2d.apply(x, w, int(padding[0]), int(padding[1]), int(stats_mode), cache,
+                             int(stride[0]), int(stride[1]))
     return y, (stats if stats.numel() else None)
+
+
+class _FactorizedReduceConv(torch.autograd.Function):
+    """The two offset 1x1 stride-2 convolutions of AmoebaNet's ``FactorizedReduce`` (reference
+    ``benchmarks/models/amoebanet/operations.py:24-40``) and their channel concatenation.
+
+    ``conv1`` reads the pixels (2i, 2j); ``conv2`` - applied in the reference to the input
+    shifted by one pixel and zero-padded at the far edge - reads (2i+1, 2j+1), which is a 1x1
+    stride-2 convolution with padding -1. Each writes its half of the channels of one output
+    tensor, so there is no shifted copy and no ``torch.cat``; backward reads the halves of dY
+    in place, and the two data gradients fill disjoint pixel classes of one dX.
+    Returns ``(out, stats [K,2])`` (per-channel sum / sum of squares for the following BN)."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor, w1: Tensor, w2: Tensor, cache1: dict, cache2: dict):  # type: ignore[override]
+        x, w1, w2 = _cl(x), _cl(w1), _cl(w2)
+        N, C, H, W = x.shape
+        k1, k2 = w1.size(0), w2.size(0)
+        Ho, Wo = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+        out = torch.empty((N, k1 + k2, Ho, Wo), device=x.device, dtype=torch.float32,
+                          memory_format=_CL)
+        if H < 2 or W < 2:
+            out[:, k1:].zero_()         # conv2 sees only padding
+        _, s1 = conv2d_forward(x, w1, (0, 0), 2, (2, 2), out=out[:, :k1])
+        if H >= 2 and W >= 2:
+            _, s2 = conv2d_forward(x, w2, (-1, -1), 2, (2, 2), out=out[:, k1:],
+                                   out_hw=(Ho, Wo))
+        else:
+            s2 = torch.zeros((k2, 2), device=x.device, dtype=torch.float32)
+        ctx.save_for_backward(x, w1, w2)
+        ctx.caches = (cache1, cache2)
+        stats = torch.cat([s1, s2], dim=0)
+        ctx.mark_non_differentiable(stats)
+        return out, stats
+
+    @staticmethod
+    def backward(ctx, dout: Tensor, _dstats):  # type: ignore[override]
+        x, w1, w2 = ctx.saved_tensors
+        k1 = w1.size(0)
+        dout = _cl(dout)
+        dy1, dy2 = dout[:, :k1], dout[:, k1:]
+        dx = dw1 = dw2 = None
+        if ctx.needs_input_grad[1]:
+            dw1 = _conv2d_wgrad(dy1, x, w1.shape, (0, 0), (2, 2))
+        if ctx.needs_input_grad[2]:
+            dw2 = _conv2d_wgrad(dy2, x, w2.shape, (-1, -1), (2, 2), fixed_hw=True)
+        if ctx.needs_input_grad[0]:
+            dx = torch.zeros_like(x, memory_format=_CL)
+            conv2d_dgrad(dy1, w1, x.shape, (0, 0), (2, 2), ctx.caches[0], out=dx,
+                         keep_untouched=True)
+            if x.size(2) >= 2 and x.size(3) >= 2:
+                conv2d_dgrad(dy2, w2, x.shape, (-1, -1), (2, 2), ctx.caches[1], out=dx,
+                             keep_untouched=True, fixed_hw=True)
+        return dx, dw1, dw2, None, None
+
+
+def factorized_reduce_conv(x: Tensor, w1: Tensor, w2: Tensor, cache1: dict, cache2: dict,
+                           ) -> Tuple[Tensor, Tensor]:
+    """``cat([conv1x1_s2(x, w1), conv1x1_s2(shift(x), w2)], 1)`` and its BN statistics."""
+    return _FactorizedReduceConv.apply(x, w1, w2, cache1, cache2)
+
+
+# ---------------------------------------------------------------- small-channel stem and head
+def _stem_weight(w: Tensor) -> Tensor:
+    """``[K,C,R,S]`` -> ``[K,R,32]`` with entry ``4*s + c`` (zero padded)."""
+    K, C, R, S = w.shape
+    wv = torch.zeros((K, R, 8, 4), device=w.device, dtype=torch.float32)
+    wv[:, :, :S, :C] = w.detach().permute(0, 2, 3, 1)
+    return wv.view(K, R, 32)
+
+
+class _StemConv2d(torch.autograd.Function):
+    """Convolution of an image with 1-4 channels (any layout) on the packed-window tcgen05 path
+    (``csrc/conv_small.cu``). Saves the packed image (4 channels, zero halo) for the weight
+    gradient; the data gradient (rarely needed: the input is data) uses ATen."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor, w: Tensor, ph: int, pw: int, sh: int, sw: int,  # type: ignore[override]
+                stats_mode: int, cache: Optional[dict], relu_input: bool = False):
+        lib = _lib.require()
+        N, C, H, W = x.shape
+        K, _, R, S = w.shape
+        Ho, Wo = _out_hw(H, W, R, S, (ph, pw), (sh, sw))
+        assert not (relu_input and x.requires_grad), 'relu_input is for data inputs'
+
+        Hp, Wp = H + 2 * ph, W + 2 * pw - S + 8
+        xp = torch.empty((N, Hp, Wp, 4), device=x.device, dtype=torch.float32)
+        wv = None
+        if cache is not None and cache.get('stem_version') == w._version \
+                and cache.get('stem_ptr') == w.data_ptr():
+            wv = cache['stem_w']
+        if wv is None:
+            fresh = _stem_weight(w)
+            wv = cache.get('stem_w') if cache is not None else None
+            if wv is not None and wv.shape == fresh.shape and wv.device == fresh.device:
+                wv.copy_(fresh)         # keep the address (captured graphs read it)
+            else:
+                wv = fresh
+            if cache is not None:
+                cache['stem_version'], cache['stem_ptr'], cache['stem_w'] = \
+                    w._version, w.data_ptr(), wv
+        y = torch.empty((N, K, Ho, Wo), device=x.device, dtype=torch.float32, memory_format=_CL)
+        stats = None
+        if stats_mode == 1:
+            stats = torch.zeros((N, K, 2), device=x.device, dtype=torch.float32)
+        elif stats_mode == 2:
+            stats = torch.zeros((K, 2), device=x.device, dtype=torch.float32)
+        with torch.cuda.device(x.device):
+            st = _lib.stream_ptr(x.device)
+            rc = lib.tgb_stem_pack(_lib.ptr(x), _lib.ptr(xp), _c_int(N), _c_int(C), _c_int(H),
+                                   _c_int(W), _c_ll(x.stride(0)), _c_ll(x.stride(1)),
+                                   _c_ll(x.stride(2)), _c_ll(x.stride(3)), _c_int(ph), _c_int(pw),
+                                   _c_int(Hp), _c_int(Wp), _c_int(int(relu_input)), st)
+            _lib.check(rc, 'tgb_stem_pack')
+            rc = lib.tgb_conv2d_stem_fprop_tf32(_lib.ptr(xp), _lib.ptr(wv), _lib.ptr(y),
+                                                _lib.ptr(stats), _c_int(N), _c_int(Hp),
+                                                _c_int(Wp), _c_int(K), _c_int(R), _c_int(sh),
+                                                _c_int(sw), _c_int(stats_mode), st)
+            _lib.check(rc, 'tgb_conv2d_stem_fprop_tf32')
+        ctx.save_for_backward(xp, w, x if x.requires_grad else x.new_empty(0))
+        ctx.geom = (N, C, H, W, K, R, S, ph, pw, sh, sw, Hp, Wp)
+        if stats is None:
+            stats = x.new_empty(0)
+        ctx.mark_non_differentiable(stats)
+        return y, stats
+
+    @staticmethod
+    def backward(ctx, dy: Tensor, _dstats):  # type: ignore[override]
+        lib = _lib.require()
+        lib.tgb_conv2d_stem_wgrad_scratch_bytes.restype = _c_ll
+        xp, w, x = ctx.saved_tensors
+        N, C, H, W, K, R, S, ph, pw, sh, sw, Hp, Wp = ctx.geom
+        dy = _cl(dy)
+        dx = dw = None
+        if ctx.needs_input_grad[1]:
+            geom = (_c_int(N), _c_int(Hp), _c_int(Wp), _c_int(K), _c_int(R), _c_int(sh),
+                    _c_int(sw))
+            need = lib.tgb_conv2d_stem_wgrad_scratch_bytes(*geom)
+            if need < 0:
+                _lib.check(1, 'tgb_conv2d_stem_wgrad_scratch_bytes')
+            scratch = torch.empty(need // 4, device=dy.device, dtype=torch.float32) \
+                if need else None
+            dwv = torch.empty((K, R, 32), device=dy.device, dtype=torch.float32)
+            with torch.cuda.device(dy.device):
+                rc = lib.tgb_conv2d_stem_wgrad_tf32(_lib.ptr(dy), _lib.ptr(xp), _lib.ptr(dwv),
+                                                    _lib.ptr(scratch), _c_ll(need), *geom,
+                                                    _lib.stream_ptr(dy.device))
+            _lib.check(rc, 'tgb_conv2d_stem_wgrad_tf32')
+            dw = dwv.view(K, R, 8, 4)[:, :, :S, :C].permute(0, 3, 1, 2).contiguous(
+                memory_format=_CL)
+        if ctx.needs_input_grad[0]:
+            dx = torch.nn.grad.conv2d_input((N, C, H, W), w, dy, stride=(sh, sw),
+                                            padding=(ph, pw))
+        return dx, dw, None, None, None, None, None, None, None
+
+
+def stem_conv2d(x: Tensor, w: Tensor, padding: Tuple[int, int], stride: Tuple[int, int] = (1, 1),
+                stats_mode: int = 0, cache: Optional[dict] = None, relu_input: bool = False,
+                ) -> Tuple[Tensor, Optional[Tensor]]:
+    """Convolution of a 1-4 channel image (NCHW or channels-last, fp32 CUDA) with filter rows of
+    at most 8 taps, on the packed-window tcgen05 path. Returns ``(y, stats or None)``.
+    ``relu_input``: convolve ``relu(x)`` (folded into the packing pass; ``x`` must be data)."""
+    assert x.size(1) <= 4 and w.size(3) <= 8 and padding[0] >= 0 and padding[1] >= 0
+    y, stats = _StemConv2d.apply(x, w, int(padding[0]), int(padding[1]), int(stride[0]),
+                                 int(stride[1]), int(stats_mode), cache, bool(relu_input))
+    return y, (stats if stats.numel() else None)
+
+
+class _HeadConv(torch.autograd.Function):
+    """1x1 convolution to at most 4 output channels (+ bias): a streaming dot product."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor, w: Tensor, bias: Optional[Tensor]):  # type: ignore[override]
+        lib = _lib.require()
+        x = _cl(x)
+        N, C, H, W = x.shape
+        K = w.size(0)
+        w2 = w.detach().reshape(K, C).contiguous()
+        y = torch.empty((N, K, H, W), device=x.device, dtype=torch.float32, memory_format=_CL)
+        with torch.cuda.device(x.device):
+            rc = lib.tgb_head_fwd(_lib.ptr(x), _lib.ptr(w2), _lib.ptr(bias), _lib.ptr(y),
+                                  _c_ll(N * H * W), _c_int(C), _c_int(K),
+                                  _lib.stream_ptr(x.device))
+        _lib.check(rc, 'tgb_head_fwd')
+        ctx.save_for_backward(x, w2)
+        ctx.w_shape = tuple(w.shape)
+        ctx.has_bias = bias is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy: Tensor):  # type: ignore[override]
+        lib = _lib.require()
+        x, w2 = ctx.saved_tensors
+        N, C, H, W = x.shape
+        K = w2.size(0)
+        dy = _cl(dy)
+        need_dx, need_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        need_db = ctx.has_bias and ctx.needs_input_grad[2]
+        dx = torch.empty_like(x, memory_format=_CL) if need_dx else None
+        dw = torch.empty((K, C), device=x.device, dtype=torch.float32) if need_dw else None
+        db = torch.empty(K, device=x.device, dtype=torch.float32) if need_db else None
+        with torch.cuda.device(x.device):
+            rc = lib.tgb_head_bwd(_lib.ptr(dy), _lib.ptr(x), _lib.ptr(w2), _lib.ptr(dx),
+                                  _lib.ptr(dw), _lib.ptr(db), _c_ll(N * H * W), _c_int(C),
+                                  _c_int(K), _lib.stream_ptr(x.device))
+        _lib.check(rc, 'tgb_head_bwd')
+        if dw is not None:
+            dw = dw.view(ctx.w_shape)
+        return dx, dw, db
+
+
+def head_conv2d(x: Tensor, w: Tensor, bias: Optional[Tensor] = None) -> Tensor:
+    """``F.conv2d(x, w, bias)`` for a 1x1 filter with 1-4 output channels (``C % 4 == 0``)."""
+    return _HeadConv.apply(x, w, bias)
 
 
 def channel_moments(x: Tensor, per_image: bool = False) -> Tensor:

@@ -10,7 +10,7 @@ from torchgpipe_b200.ops import functional as TF
 
 __all__ = ['Absorbed', 'ConvInstNormLeaky', 'Conv2dTC', 'ConvBatchNormAct', 'AbsorbedBatchNorm2d',
            'MaxPool2x2', 'UpsamplePopCat', 'LinearTC', 'Pool2dNHWC', 'GlobalAvgPoolNHWC',
-           'BatchNormResidualAct']
+           'BatchNormResidualAct', 'AmoebaStem', 'AmoebaFactorizedReduce']
 
 _CL = torch.channels_last
 
@@ -34,34 +34,62 @@ class Absorbed(nn.Module):
         return input
 
 
+def _conv_any(x: Tensor, weight: Tensor, stride, padding, stats_mode: int, cache: dict):
+    """``(y, stats)`` of a bias-free convolution on whichever native path covers it
+    (``TF.conv_kind``): implicit GEMM, packed-window stem, or - statistics by the moments
+    kernel - the streaming head. ``None`` when no native path applies."""
+    K, C, R, S = weight.shape
+    kind = TF.conv_kind(C, K, (R, S), stride, 1, 1)
+    if kind == 'tc':
+        return TF.conv2d(x, weight, padding, stats_mode=stats_mode, cache=cache, stride=stride)
+    if kind == 'stem' and padding[0] >= 0 and padding[1] >= 0:
+        return TF.stem_conv2d(x, weight, padding, stride, stats_mode=stats_mode, cache=cache)
+    if kind == 'head' and tuple(padding) == (0, 0):
+        y = TF.head_conv2d(x, weight, None)
+        stats = None
+        if stats_mode:
+            stats = TF.channel_moments(y, per_image=stats_mode == 1) if K % 4 == 0 else None
+        return y, stats
+    return None
+
+
 class Conv2dTC(nn.Module):
-    """Stride-1 ``nn.Conv2d`` (no bias) on the tcgen05 kernels; same ``weight`` parameter."""
+    """``nn.Conv2d`` (groups 1, no dilation, strides up to 2x2) on the native kernels; same
+    ``weight`` / ``bias`` parameters. Wide layers run the tcgen05 implicit GEMM, a 1-4 channel
+    input the packed-window stem path, a 1x1 layer with at most 4 outputs the streaming head."""
 
     def __init__(self, conv: nn.Conv2d) -> None:
         super().__init__()
         self.in_channels, self.out_channels = conv.in_channels, conv.out_channels
-        self.kernel_size, self.padding = conv.kernel_size, conv.padding
+        self.kernel_size, self.padding, self.stride = conv.kernel_size, conv.padding, conv.stride
         self.weight = conv.weight
         self.weight.data = self.weight.data.contiguous(memory_format=_CL)
         self.bias = conv.bias
+        self.kind = TF.conv_kind(self.in_channels, self.out_channels, self.kernel_size,
+                                 self.stride, 1, 1)
         self._cache: dict = {}
 
     def refresh_derived_weights(self) -> None:
-        """Updates the cached dgrad weights in place after an optimiser step (CUDA-graph mode)."""
+        """Updates the cached derived weights in place after an optimiser step (graph mode)."""
         TF.refresh_dgrad_weight(self.weight, self._cache)
+        TF.refresh_stem_weight(self.weight, self._cache)
 
     def extra_repr(self) -> str:
         return (f'{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, '
-                f'padding={self.padding}, tcgen05/tf32')
+                f'stride={self.stride}, padding={self.padding}, bias={self.bias is not None}, '
+                f'native={self.kind}')
 
     def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
-        if input.is_cuda and input.dtype == torch.float32 and TF.conv_supported(
-                self.in_channels, self.out_channels, 1, 1, 1):
-            y, _ = TF.conv2d(input, self.weight, self.padding, cache=self._cache)
-            if self.bias is not None:
-                y = y + self.bias.view(1, -1, 1, 1)
-            return y
-        return F.conv2d(input, self.weight, self.bias, padding=self.padding)
+        if input.is_cuda and input.dtype == torch.float32 and self.kind is not None:
+            if self.kind == 'head' and tuple(self.padding) == (0, 0):
+                return TF.head_conv2d(input, self.weight, self.bias)
+            got = _conv_any(input, self.weight, self.stride, self.padding, 0, self._cache)
+            if got is not None:
+                y = got[0]
+                if self.bias is not None:
+                    y = TF.add_channel_bias(y, self.bias)
+                return y
+        return F.conv2d(input, self.weight, self.bias, self.stride, self.padding)
 
 
 class ConvInstNormLeaky(nn.Module):
@@ -77,7 +105,7 @@ class ConvInstNormLeaky(nn.Module):
     def __init__(self, conv: nn.Conv2d, p: float, eps: float, slope: float) -> None:
         super().__init__()
         self.in_channels, self.out_channels = conv.in_channels, conv.out_channels
-        self.kernel_size, self.padding = conv.kernel_size, conv.padding
+        self.kernel_size, self.padding, self.stride = conv.kernel_size, conv.padding, conv.stride
         self.weight = conv.weight
         self.weight.data = self.weight.data.contiguous(memory_format=_CL)
         self.p, self.eps, self.slope = float(p), float(eps), float(slope)
@@ -89,8 +117,9 @@ class ConvInstNormLeaky(nn.Module):
                 f'leaky={self.slope}, tcgen05/tf32')
 
     def refresh_derived_weights(self) -> None:
-        """Updates the cached dgrad weights in place after an optimiser step (CUDA-graph mode)."""
+        """Updates the cached derived weights in place after an optimiser step (graph mode)."""
         TF.refresh_dgrad_weight(self.weight, self._cache)
+        TF.refresh_stem_weight(self.weight, self._cache)
 
     def _drop_scale(self, n: int, device: torch.device) -> Optional[Tensor]:
         if not self.training or self.p == 0.0:
@@ -100,18 +129,16 @@ class ConvInstNormLeaky(nn.Module):
 
     def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
         if not (input.is_cuda and input.dtype == torch.float32):
-            y = F.conv2d(input, self.weight, None, padding=self.padding)
+            y = F.conv2d(input, self.weight, None, self.stride, self.padding)
             y = F.dropout2d(y, self.p, self.training)
             return F.leaky_relu(F.instance_norm(y, eps=self.eps), self.slope)
 
         scale = self._drop_scale(input.size(0), input.device)
-        if TF.conv_supported(self.in_channels, self.out_channels, 1, 1, 1):
-            y, stats = TF.conv2d(input, self.weight, self.padding, stats_mode=1,
-                                 cache=self._cache)
-        else:
-            # e.g. the 3-channel stem: library convolution, statistics by the moments kernel
+        got = _conv_any(input, self.weight, self.stride, self.padding, 1, self._cache)
+        if got is None:         # no native path (odd output channels): library convolution
             x = input.contiguous(memory_format=_CL)
-            y, stats = F.conv2d(x, self.weight, None, padding=self.padding), None
+            got = F.conv2d(x, self.weight, None, self.stride, self.padding), None
+        y, stats = got
         return TF.instnorm_leaky(y, stats, scale, self.eps, self.slope)
 
 
@@ -220,6 +247,7 @@ class ConvBatchNormAct(nn.Module):
 
     def refresh_derived_weights(self) -> None:
         TF.refresh_dgrad_weight(self.weight, self._cache)
+        TF.refresh_stem_weight(self.weight, self._cache)
 
     def extra_repr(self) -> str:
         return (f'{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, '
@@ -242,14 +270,12 @@ class ConvBatchNormAct(nn.Module):
             y = _bn_torch(bn, y)
             return F.relu(y) if self.relu else y
 
-        if self.stride == (1, 1) and TF.conv_supported(self.in_channels, self.out_channels,
-                                                       1, 1, 1):
-            y, stats = TF.conv2d(input, self.weight, self.padding, stats_mode=2,
-                                 cache=self._cache)
-        else:
-            # strided / odd-channel convolutions: library kernel, statistics by tgb_moments
+        got = _conv_any(input, self.weight, self.stride, self.padding, 2, self._cache)
+        if got is None:         # no native path: library kernel, statistics by tgb_moments
             x = input.contiguous(memory_format=_CL)
-            y = F.conv2d(x, self.weight, None, self.stride, self.padding)
+            got = F.conv2d(x, self.weight, None, self.stride, self.padding), None
+        y, stats = got
+        if stats is None:
             stats = TF.channel_moments(y)
         if self.defer:
             return y, stats
@@ -258,6 +284,81 @@ class ConvBatchNormAct(nn.Module):
                                                                y.numel() // y.size(1))
         return TF.batchnorm_act(y, stats, bn.weight, bn.bias, running_mean, running_var, bn.eps,
                                 momentum, self.relu)
+
+
+def _bn_apply(bn: AbsorbedBatchNorm2d, y: Tensor, stats: Optional[Tensor], relu: bool) -> Tensor:
+    """Training-mode BatchNorm(+ReLU) of ``y`` from epilogue statistics, with ``bn``'s running
+    estimates (or DeferredBatchNorm accumulators) kept up to date."""
+    if stats is None:
+        stats = TF.channel_moments(y)
+    running_mean, running_var, momentum = _bn_running_args(bn, stats, y.numel() // y.size(1))
+    return TF.batchnorm_act(y, stats, bn.weight, bn.bias, running_mean, running_var, bn.eps,
+                            momentum, relu)
+
+
+class AmoebaStem(nn.Module):
+    """AmoebaNet's ``Stem`` (``relu -> conv3x3/2 (3 channels in) -> bn``, reference
+    ``benchmarks/models/amoebanet/__init__.py:47-58``) on the packed-window stem kernels: the
+    ReLU of the image is folded into the packing pass, the BatchNorm statistics come from the
+    convolution's epilogue. Children keep their names (``relu``, ``conv``, ``bn``)."""
+
+    def __init__(self, stem: nn.Module) -> None:
+        super().__init__()
+        self.relu, self.conv, self.bn = stem.relu, stem.conv, stem.bn
+        self.bn.__class__ = AbsorbedBatchNorm2d
+        self._cache: dict = {}
+
+    def refresh_derived_weights(self) -> None:
+        TF.refresh_stem_weight(self.conv.weight, self._cache)
+
+    def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
+        conv, bn = self.conv, self.bn
+        native = (input.is_cuda and input.dtype == torch.float32 and bn.training
+                  and not input.requires_grad
+                  and TF.conv_kind(conv.in_channels, conv.out_channels, conv.kernel_size,
+                                   conv.stride, conv.dilation, conv.groups) == 'stem')
+        if not native:
+            y = F.conv2d(F.relu(input), conv.weight, None, conv.stride, conv.padding)
+            return _bn_torch(bn, y)
+        y, stats = TF.stem_conv2d(input, conv.weight, conv.padding, conv.stride, stats_mode=2,
+                                  cache=self._cache, relu_input=True)
+        return _bn_apply(bn, y, stats, relu=False)
+
+
+class AmoebaFactorizedReduce(nn.Module):
+    """AmoebaNet's ``FactorizedReduce`` (reference ``amoebanet/operations.py:24-40``): ReLU, two
+    offset 1x1 stride-2 convolutions writing the two channel halves of one tensor (no shifted
+    copy, no concatenation), BatchNorm from the epilogue statistics. Children keep their names
+    (``relu``, ``pad``, ``conv1``, ``conv2``, ``bn``)."""
+
+    def __init__(self, reduce: nn.Module) -> None:
+        super().__init__()
+        self.relu, self.pad = reduce.relu, reduce.pad
+        self.conv1, self.conv2, self.bn = reduce.conv1, reduce.conv2, reduce.bn
+        self.bn.__class__ = AbsorbedBatchNorm2d
+        for conv in (self.conv1, self.conv2):
+            conv.weight.data = conv.weight.data.contiguous(memory_format=_CL)
+        self._cache1: dict = {}
+        self._cache2: dict = {}
+
+    def refresh_derived_weights(self) -> None:
+        TF.refresh_dgrad_weight(self.conv1.weight, self._cache1)
+        TF.refresh_dgrad_weight(self.conv2.weight, self._cache2)
+
+    def forward(self, input: Tensor, relu_done: bool = False) -> Tensor:  # type: ignore[override]
+        bn = self.bn
+        x = input if relu_done else F.relu(input)
+        c_in, k1, k2 = self.conv1.in_channels, self.conv1.out_channels, self.conv2.out_channels
+        native = (x.is_cuda and x.dtype == torch.float32 and bn.training
+                  and c_in % 4 == 0 and k1 % 4 == 0 and k2 % 4 == 0)
+        if not native:
+            shifted = self.pad(x[:, :, 1:, 1:])
+            y = torch.cat([F.conv2d(x, self.conv1.weight, None, 2),
+                           F.conv2d(shifted, self.conv2.weight, None, 2)], dim=1)
+            return _bn_torch(bn, y)
+        y, stats = TF.factorized_reduce_conv(x, self.conv1.weight, self.conv2.weight,
+                                             self._cache1, self._cache2)
+        return _bn_apply(bn, y, stats, relu=False)
 
 
 class MaxPool2x2(nn.Module):
