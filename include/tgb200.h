@@ -151,6 +151,86 @@ int tgb_conv2d_fprop_plan(int N, int H, int W, int C, int K, int R, int S, int p
  * convolution is then tgb_conv2d_fprop_tf32(dy, wt). */
 int tgb_dgrad_weight(const float* w, float* wt, int K, int C, int R, int S, cudaStream_t stream);
 
+/* Strided convolutions (strides 1 or 2 per axis, any integer padding; negative = crop).
+ *   y[n,ho,wo,k] = sum x[n, sh*ho+r-pad_h, sw*wo+s-pad_w, c] * w[k,r,s,c]
+ * Ho, Wo = 0: output extent from the usual arithmetic; > 0: compute exactly that extent (padding
+ * that differs between the near and the far edge; what lies outside x reads as zero).
+ * y_pixel_stride (elements): K, or larger when y is a channel slice of a wider NHWC tensor - a
+ * concatenation written in place. The epilogue statistics work as for tgb_conv2d_fprop_tf32.
+ * Reference call sites: benchmarks/models/resnet/__init__.py:41 (1x1/2 projection),
+ * resnet/bottleneck.py:22,28 (3x3/2), amoebanet/__init__.py:28 and operations.py:71-84 (1x7, 7x1,
+ * 3x3, 1x1 with stride), operations.py:31-32 (FactorizedReduce: two offset 1x1/2, the second one
+ * is pad = -1 with the extent of the first) - cuDNN in the reference. */
+int tgb_conv2d_fprop_strided_tf32(const float* x, const float* w, float* y, float* stats,
+                                  int N, int H, int W, int C, int K, int R, int S,
+                                  int pad_h, int pad_w, int stride_h, int stride_w,
+                                  int Ho, int Wo, long long y_pixel_stride, int stats_mode,
+                                  cudaStream_t stream);
+
+/* Data gradient of the convolution above: one stride-1 launch of the forward kernel per parity
+ * class of input pixels (h mod sh, w mod sw), each reading only the filter taps that reach its
+ * class and storing through a strided view of dx.
+ * tgb_dgrad_weight_strided prepares the per-class filter banks (tap-flipped, channel-transposed,
+ * class-major in one buffer of tgb_dgrad_weight_strided_elems floats); redo it when w changes.
+ * dy_pixel_stride: K, or larger when dy is a channel slice of a wider NHWC gradient.
+ * keep_untouched != 0: input pixels no tap reads keep their contents (default: zero-filled) -
+ * lets two convolutions over disjoint pixel classes of one input share one dx.
+ * Ho_given / Wo_given: as Ho / Wo above (0 = derive). */
+long long tgb_dgrad_weight_strided_elems(int K, int C, int R, int S, int pad_h, int pad_w,
+                                         int stride_h, int stride_w);
+int tgb_dgrad_weight_strided(const float* w, float* out, int K, int C, int R, int S,
+                             int pad_h, int pad_w, int stride_h, int stride_w,
+                             cudaStream_t stream);
+int tgb_conv2d_dgrad_tf32(const float* dy, const float* wt_classes, float* dx,
+                          int N, int H, int W, int C, int K, int R, int S, int pad_h, int pad_w,
+                          int stride_h, int stride_w, int Ho_given, int Wo_given,
+                          long long dy_pixel_stride, int keep_untouched, cudaStream_t stream);
+
+/* Weight gradient of the strided convolution (per-tap kernel; arguments as
+ * tgb_conv2d_wgrad_tf32 plus strides, optional fixed output extent and dy pixel stride). */
+long long tgb_conv2d_wgrad_strided_scratch_bytes(int N, int H, int W, int C, int K, int R, int S,
+                                                 int pad_h, int pad_w, int stride_h,
+                                                 int stride_w, int Ho, int Wo,
+                                                 long long dy_pixel_stride);
+int tgb_conv2d_wgrad_strided_tf32(const float* dy, const float* x, float* dw, float* scratch,
+                                  long long scratch_bytes, int N, int H, int W, int C, int K,
+                                  int R, int S, int pad_h, int pad_w, int stride_h, int stride_w,
+                                  int Ho, int Wo, long long dy_pixel_stride, int accumulate,
+                                  cudaStream_t stream);
+
+/* Input stem: convolution of an image with 1-4 channels and filter rows of at most 8 taps.
+ * tgb_stem_pack copies src (any layout: element strides s_n, s_c, s_h, s_w) into
+ * dst [N][Hp][Wp][4], Hp = H + 2*pad_h, Wp = W + 2*pad_w - S + 8, zero in the halo and in the
+ * missing channels; relu != 0 stores max(x, 0) (AmoebaNet's stem). In that buffer every run of 8
+ * pixels is one 128-byte K block, which an overlapping-window tensor map (pixel stride 16 bytes,
+ * innermost extent 128 bytes) feeds to the ordinary tcgen05 kernels: an R x S filter becomes an
+ * R x 1 filter over 32 "channels" 4*s + c, wv [K][R][32] (zero where s >= S or c >= C).
+ * Forward: y [N][Ho][Wo][K] (+ statistics as above). Weight gradient: dwv [K][R][32], entries of
+ * taps / channels that do not exist are meaningless.
+ * Reference call sites: resnet/__init__.py:55 (7x7/2), amoebanet/__init__.py:54 (3x3/2),
+ * unet/__init__.py:44 first cell (3x3) - cuDNN in the reference. */
+int tgb_stem_pack(const float* src, float* dst, int N, int C, int H, int W,
+                  long long s_n, long long s_c, long long s_h, long long s_w,
+                  int pad_h, int pad_w, int Hp, int Wp, int relu, cudaStream_t stream);
+int tgb_conv2d_stem_fprop_tf32(const float* xp, const float* wv, float* y, float* stats,
+                               int N, int Hp, int Wp, int K, int R, int stride_h, int stride_w,
+                               int stats_mode, cudaStream_t stream);
+long long tgb_conv2d_stem_wgrad_scratch_bytes(int N, int Hp, int Wp, int K, int R,
+                                              int stride_h, int stride_w);
+int tgb_conv2d_stem_wgrad_tf32(const float* dy, const float* xp, float* dwv, float* scratch,
+                               long long scratch_bytes, int N, int Hp, int Wp, int K, int R,
+                               int stride_h, int stride_w, cudaStream_t stream);
+
+/* 1x1 convolution to 1-4 output channels (C % 4 == 0), plain fp32: y[p][k] = x[p][:] . w[k][:]
+ * + bias[k] over `pixels` = N*H*W NHWC pixels; backward writes dx (may be NULL), and overwrites
+ * dw [K][C] and db [K] (either may be NULL; x may be NULL when dw is). A streaming kernel: one
+ * pass over x forward, one pass over x and one write of dx backward.
+ * Reference call site: unet/__init__.py:138 (64 -> 1 head; cuDNN in the reference). */
+int tgb_head_fwd(const float* x, const float* w, const float* bias, float* y,
+                 long long pixels, int C, int K, cudaStream_t stream);
+int tgb_head_bwd(const float* dy, const float* x, const float* w, float* dx, float* dw, float* db,
+                 long long pixels, int C, int K, cudaStream_t stream);
+
 /* NHWC fp32 pooling family and residual joins (C multiple of 4; n multiple of 4).
  * tgb_pool2d_fwd/bwd: k x k window, stride s, zero padding p (2p <= k), floor output size.
  *   mode 0 max, 1 average over the valid (non-padding) pixels (count_include_pad=False),

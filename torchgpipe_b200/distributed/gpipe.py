@@ -167,27 +167,34 @@ class DistributedGPipe:
                  checkpoint: str = 'never',
                  transport: Optional[Transport] = None,
                  cuda_graphs: bool = False,
+                 partitions: Optional[List[nn.Sequential]] = None,
                  ) -> None:
         microbatch_chunks = int(microbatch_chunks)
         checkpoint = str(checkpoint)
 
-        if balance is None:
+        if balance is None and partitions is None:
             raise ValueError(recommend_auto_balance('balance is required'))
         if microbatch_chunks <= 0:
             raise ValueError('number of chunks must be positive integer')
         if checkpoint not in ('always', 'except_last', 'never'):
             raise ValueError("checkpoint is not one of 'always', 'except_last', or 'never'")
 
-        verify_module(module)
-        verify_skippables(module)
-        balance = list(balance)
-        try:
-            check_balance(module, balance)
-        except BalanceError as exc:
-            raise ValueError(recommend_auto_balance(str(exc)))
+        if partitions is not None:
+            # stages that already exist, each on its device (the single-process GPipe hands its
+            # own partitions over when it runs them through this engine): nothing to split
+            stages = list(partitions)
+            balance = [len(s) for s in stages]
+        else:
+            verify_module(module)
+            verify_skippables(module)
+            balance = list(balance)
+            try:
+                check_balance(module, balance)
+            except BalanceError as exc:
+                raise ValueError(recommend_auto_balance(str(exc)))
+            stages = [nn.Sequential(s) for s in _stage_slices(module, balance)]
 
         # Skip routes are numbered in model order, identically on every rank.
-        stages = [nn.Sequential(s) for s in _stage_slices(module, balance)]
         layout = inspect_skip_layout(stages)
         order: Dict[SkipKey, int] = {}
         for stage in stages:
@@ -201,7 +208,10 @@ class DistributedGPipe:
         self._routes_out = [(slot, dst, key) for slot, src, dst, key in routes if src == rank]
         self._routes_in = [(slot, src, key) for slot, src, dst, key in routes if dst == rank]
 
-        partition = get_module_partition(module, rank, balance, device)
+        if partitions is not None:
+            partition = stages[rank]
+        else:
+            partition = get_module_partition(module, rank, balance, device)
         if deferred_batch_norm:
             partition = DeferredBatchNorm.convert_deferred_batch_norm(partition, microbatch_chunks)
         self.module = partition
@@ -478,14 +488,17 @@ class DistributedGPipe:
         return t
 
     # -- backward ------------------------------------------------------------------
-    def backward(self, losses: Optional[List[Tensor]]) -> None:
+    def backward(self, losses: Optional[List[Tensor]],
+                 output_grads: Optional[List[TensorOrTensors]] = None) -> None:
         """Back-propagates every micro-batch (latest first) and passes gradients upstream.
 
-        The last rank passes its per-micro-batch losses; other ranks pass
-        ``None`` and receive output gradients from the next stage.
+        The last rank passes its per-micro-batch losses - or, instead, the gradients of its
+        per-micro-batch outputs as ``output_grads`` (one tensor or tuple per micro-batch; used
+        when the loss is computed outside, on the gathered output); other ranks pass ``None``
+        and receive output gradients from the next stage.
         """
         tp = self.transport
-        if losses is not None:
+        if losses is not None or output_grads is not None:
             assert self.is_last, 'only the last stage takes losses'
         for staged in self._graphed.values():
             staged.refresh_derived_weights()     # once per step, outside the graphs
@@ -498,7 +511,7 @@ class DistributedGPipe:
             stashes = produced[flight.n_outputs:]
 
             if flight.staged is not None:
-                self._graphed_backward(mb, flight, losses)
+                self._graphed_backward(mb, flight, losses, output_grads)
                 self._flights[mb] = None
                 self._outputs[mb] = None
                 continue
@@ -508,6 +521,12 @@ class DistributedGPipe:
             if losses is not None:
                 roots.append(losses[mb])
                 grads.append(None)
+            elif output_grads is not None:
+                given = output_grads[mb]
+                for y, g in zip(outs, (given,) if torch.is_tensor(given) else given):
+                    if y.requires_grad and g is not None:
+                        roots.append(y)
+                        grads.append(g)
             else:
                 received = tp.recv(self.rank + 1, ('bwd', mb, 0),
                                    like=outs[0] if flight.atomic else outs)
@@ -559,7 +578,8 @@ class DistributedGPipe:
             self._graphed[key] = staged
         return staged
 
-    def _graphed_backward(self, mb: int, flight: _Flight, losses: Optional[List[Tensor]]) -> None:
+    def _graphed_backward(self, mb: int, flight: _Flight, losses: Optional[List[Tensor]],
+                          output_grads: Optional[List[TensorOrTensors]] = None) -> None:
         tp = self.transport
         produced = flight.outputs
         outs = produced[:flight.n_outputs]
@@ -570,6 +590,9 @@ class DistributedGPipe:
             if losses[mb].requires_grad:
                 losses[mb].backward()
             gouts.extend(y.grad for y in outs)
+        elif output_grads is not None:
+            given = output_grads[mb]
+            gouts.extend((given,) if torch.is_tensor(given) else given)
         else:
             received = tp.recv(self.rank + 1, ('bwd', mb, 0),
                                like=outs[0] if flight.atomic else outs)

@@ -148,6 +148,16 @@ class GPipe(nn.Module):
         checkpoint: ``'always'``, ``'except_last'`` (default) or ``'never'``.
         deferred_batch_norm: track BatchNorm running statistics per mini-batch
             instead of per micro-batch.
+        cuda_graphs: replay every stage pass from CUDA graphs
+            (:mod:`torchgpipe_b200.runtime.graph_pipeline`): one graph launch per
+            micro-batch and stage instead of hundreds of kernel launches, which is
+            what keeps B200-class devices busy at the published micro-batch
+            counts. Same call pattern (``out = model(x); loss(out).backward()``);
+            parameter gradients arrive in ``param.grad``. Needs CUDA devices,
+            static micro-batch shapes and host-sync-free layers; every
+            micro-batch is recomputed from its stage input (``checkpoint`` then
+            only names the memory behaviour you get anyway), the pipeline input
+            receives no gradient, and ``deferred_batch_norm`` is refused.
 
     Raises:
         TypeError: ``module`` is not ``nn.Sequential`` / skips do not match.
@@ -172,6 +182,7 @@ class GPipe(nn.Module):
                  chunks: int = chunks,
                  checkpoint: str = checkpoint,
                  deferred_batch_norm: bool = False,
+                 cuda_graphs: bool = False,
                  ) -> None:
         super().__init__()
 
@@ -191,6 +202,11 @@ class GPipe(nn.Module):
         self.chunks = chunks
         self.checkpoint = checkpoint
 
+        if deferred_batch_norm and cuda_graphs:
+            raise ValueError(
+                'cuda_graphs=True cannot be combined with deferred_batch_norm=True: the '
+                'micro-batch counter and the commit of the accumulated statistics are host-side '
+                'state that a graph replay does not execute')
         if deferred_batch_norm:
             module = DeferredBatchNorm.convert_deferred_batch_norm(module, chunks)
 
@@ -210,6 +226,11 @@ class GPipe(nn.Module):
         self._executors: Optional[ExecutorPool] = None
         #: Set to a :class:`Timeline` to record per-cell CUDA events.
         self.timeline: Optional[Timeline] = None
+        #: Whether stage passes are replayed from CUDA graphs (see the class docstring).
+        self.cuda_graphs = bool(cuda_graphs)
+        if self.cuda_graphs and any(d.type != 'cuda' for d in self.devices):
+            raise ValueError('cuda_graphs=True needs every partition on a CUDA device')
+        self._graph_engine: Any = None
 
     # -- sequence protocol over the ORIGINAL layers ---------------------------
     def __len__(self) -> int:
@@ -303,6 +324,13 @@ class GPipe(nn.Module):
         if not self.devices:
             return input        # an empty nn.Sequential is the identity
 
+        if self.cuda_graphs:
+            if self._graph_engine is None:
+                from torchgpipe_b200.runtime.graph_pipeline import GraphedPipeline
+                self._graph_engine = GraphedPipeline(self.partitions, self.devices, self.chunks,
+                                                     self.checkpoint)
+            return self._graph_engine(input)
+
         batches = microbatch.scatter(input, self.chunks)
         pipeline = Pipeline(batches,
                             self.partitions,
@@ -328,6 +356,7 @@ def _gpipe_getstate(self: GPipe) -> Dict[str, Any]:
     state = dict(self.__dict__)
     state['_copy_streams'] = None
     state['_executors'] = None
+    state['_graph_engine'] = None
     state['timeline'] = None
     return state
 

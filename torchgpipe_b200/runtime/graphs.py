@@ -139,7 +139,9 @@ class GraphedStage:
                 self._pool = torch.cuda.graph_pool_handle()
 
             before = ops.launch_count()
-            with torch.cuda.graph(cap.fwd, pool=self._pool):
+            # thread_local: other threads of this process (the stages of a single-process
+            # pipeline on other devices) keep allocating and launching while this one records
+            with torch.cuda.graph(cap.fwd, pool=self._pool, capture_error_mode='thread_local'):
                 with torch.set_grad_enabled(grad):
                     cap.static_outputs = tuple(self.function(tuple(cap.static_inputs)))
             cap.native_launches_fwd = ops.launch_count() - before
@@ -150,7 +152,8 @@ class GraphedStage:
                     (diff_inputs or self.params):
                 cap.bwd = torch.cuda.CUDAGraph()
                 before = ops.launch_count()
-                with torch.cuda.graph(cap.bwd, pool=self._pool):
+                with torch.cuda.graph(cap.bwd, pool=self._pool,
+                                      capture_error_mode='thread_local'):
                     grads = run_backward(cap.static_outputs, cap.static_grad_outputs)
                 cap.native_launches_bwd = ops.launch_count() - before
                 n_in = len(diff_inputs)
