@@ -42,6 +42,8 @@ def main():
     p.add_argument('--devices', type=str, default=None, help='e.g. "0,1,2,3" or "cpu,cpu"')
     p.add_argument('--balance', default='reference', help='"reference" or "auto" (balance_by_time)')
     p.add_argument('--no-kernels', action='store_true')
+    p.add_argument('--graphs', action='store_true',
+                   help='ours: GPipe(cuda_graphs=True), every stage pass replayed from CUDA graphs')
     p.add_argument('--smoke', action='store_true', help='tiny model / batch (plumbing check)')
     p.add_argument('--out', default=None, help='append the JSON line to this file')
     args = p.parse_args()
@@ -80,11 +82,12 @@ def main():
             from torchgpipe_b200.balance import balance_by_time
             sample = torch.rand(max(batch // chunks, 1), channels, hw, hw)
             balance = balance_by_time(len(balance), model, sample, device=devices[0])
+        extra = {'cuda_graphs': True} if (args.graphs and args.impl == 'ours') else {}
         pipe = GPipe(model, balance, devices=devices, chunks=chunks,
-                     checkpoint=cfg.get('checkpoint', 'except_last'))
+                     checkpoint=cfg.get('checkpoint', 'except_last'), **extra)
         in_dev, out_dev = pipe.devices[0], pipe.devices[-1]
         cfg['balance'] = list(balance)
-        if args.impl == 'ours':
+        if args.impl == 'ours' and not args.graphs:
             from torchgpipe_b200.runtime.timeline import Timeline
             timeline = Timeline()
 
@@ -110,7 +113,9 @@ def main():
               'chunks': chunks, 'balance': cfg['balance'], 'devices': [str(d) for d in used],
               'checkpoint': cfg.get('checkpoint', 'except_last'), 'steps': args.steps,
               'dtype': 'fp32 storage / tf32 conv', 'data': 'synthetic',
-              'kernels': 'sm100' if (convert is not None and not args.no_kernels) else 'torch'}
+              'kernels': 'sm100' if (convert is not None and not args.no_kernels) else 'torch',
+              'engine': 'GPipe(cuda_graphs=True)' if (args.graphs and args.impl == 'ours')
+              else 'GPipe'}
     if timeline is not None:
         pipe.timeline = timeline
         step()

@@ -307,6 +307,10 @@ class GPipe(nn.Module):
             self._executors = ExecutorPool(self.devices)
         return self._executors
 
+    def native_launches_replayed(self) -> int:
+        """Native-kernel launches issued through CUDA-graph replays so far (graph mode)."""
+        return 0 if self._graph_engine is None else self._graph_engine.native_launches_replayed()
+
     def _checkpoint_stop(self) -> int:
         if not self.training:
             return 0
