@@ -19,6 +19,7 @@ the same ``Checkpoint``/``Recompute`` pair as in single-process mode, so
 ``backward`` is a single ``torch.autograd.backward`` whose roots are the
 stage outputs and the stashed skips.
 """
+import contextlib
 from collections import OrderedDict
 from typing import Any, Dict, Iterable, Iterator, List, Optional, Tuple, Union
 
@@ -245,6 +246,11 @@ class DistributedGPipe:
         self.timeline = False
         self._marks: List[Tuple[str, Any, Any, Any]] = []
         self._bytes_received = 0
+        #: Held around everything this stage enqueues on its device for one micro-batch pass
+        #: (never while waiting for a message). A no-op unless several stages of one process
+        #: share a device: then it is one lock per device, because a CUDA-graph capture must not
+        #: overlap with work another thread puts on the same device's default stream.
+        self.device_lock: Any = contextlib.nullcontext()
 
     @staticmethod
     def _refuse_host_state_under_graphs(partition: nn.Module, deferred_batch_norm: bool) -> None:
@@ -426,59 +432,69 @@ class DistributedGPipe:
                 received = tp.recv(self.rank - 1, ('fwd', mb, 0))
                 self._count_bytes(received)
             atomic_in = torch.is_tensor(received)
-            moved = to(self.device, received)
-            boundary = tuple(self._as_leaf(t, grad_mode and not self.is_first)
-                             for t in ((moved,) if atomic_in else moved))
-            skips = []
+            raw_skips = []
             for slot, src, _ in self._routes_in:
                 t = tp.recv(src, ('skip', mb, slot))
                 self._count_bytes(t)
-                skips.append(self._as_leaf(to(self.device, t), grad_mode))
-            t1 = self._mark()
-
-            leaves = boundary + tuple(skips)
-            flight.leaves = leaves
-            flight.n_boundary = len(boundary)
-            flight.atomic_in = atomic_in
-            function = self._stage_function(len(boundary), atomic_in, flight)
-
-            if self.cuda_graphs:
-                staged = self._graphed_stage(len(boundary), atomic_in, flight)
-                flight.staged = staged
-                with nvtx.annotate(f'fwd mb{mb} stage{self.rank}'):
-                    produced, flight.rng = staged.forward(leaves)
-                flight.n_outputs, flight.atomic = staged.meta['n_outputs'], staged.meta['atomic']
-                if self.is_last and grad_mode:
-                    # the caller differentiates its loss w.r.t. these leaves; backward() feeds
-                    # their .grad to the backward graph
-                    for y in produced[:flight.n_outputs]:
-                        if y.is_floating_point():
-                            y.requires_grad_()
-            elif mb < stop:
-                with nvtx.annotate(f'fwd mb{mb} stage{self.rank} (checkpointed)'):
-                    chk = Checkpointing(function, Batch(leaves))
-                    out_batch = chk.checkpoint()
-                    chk.recompute(out_batch)
-                    produced = tuple(out_batch)
-            else:
-                with nvtx.annotate(f'fwd mb{mb} stage{self.rank}'):
-                    produced = function(leaves)
-
-            if t0 is not None:
-                self._marks.append(('fwd', t0, t1, self._mark()))
-            outs = produced[:flight.n_outputs]
-            stashes = produced[flight.n_outputs:]
-            flight.outputs = produced
-            self._flights[mb] = flight
-            self._outputs[mb] = outs[0] if flight.atomic else outs
-
-            if not self.is_last:
-                tp.send(self.rank + 1, ('fwd', mb, 0),
-                        outs[0].detach() if flight.atomic else tuple(y.detach() for y in outs))
-            for (slot, dst, _), t in zip(self._routes_out, stashes):
-                tp.send(dst, ('skip', mb, slot), t.detach())
+                raw_skips.append(t)
+            with self.device_lock:
+                self._forward_one(mb, m, stop, grad_mode, flight, received, atomic_in, raw_skips,
+                                  t0)
 
         return self._outputs[:m] if m != self.chunks else self._outputs
+
+    def _forward_one(self, mb: int, m: int, stop: int, grad_mode: bool, flight: '_Flight',
+                     received: TensorOrTensors, atomic_in: bool, raw_skips: List[Tensor],
+                     t0: Any) -> None:
+        """Everything stage-local for micro-batch ``mb`` once its inputs have arrived."""
+        tp = self.transport
+        moved = to(self.device, received)
+        boundary = tuple(self._as_leaf(t, grad_mode and not self.is_first)
+                         for t in ((moved,) if atomic_in else moved))
+        skips = [self._as_leaf(to(self.device, t), grad_mode) for t in raw_skips]
+        t1 = self._mark()
+
+        leaves = boundary + tuple(skips)
+        flight.leaves = leaves
+        flight.n_boundary = len(boundary)
+        flight.atomic_in = atomic_in
+        function = self._stage_function(len(boundary), atomic_in, flight)
+
+        if self.cuda_graphs:
+            staged = self._graphed_stage(len(boundary), atomic_in, flight)
+            flight.staged = staged
+            with nvtx.annotate(f'fwd mb{mb} stage{self.rank}'):
+                produced, flight.rng = staged.forward(leaves)
+            flight.n_outputs, flight.atomic = staged.meta['n_outputs'], staged.meta['atomic']
+            if self.is_last and grad_mode:
+                # the caller differentiates its loss w.r.t. these leaves; backward() feeds
+                # their .grad to the backward graph
+                for y in produced[:flight.n_outputs]:
+                    if y.is_floating_point():
+                        y.requires_grad_()
+        elif mb < stop:
+            with nvtx.annotate(f'fwd mb{mb} stage{self.rank} (checkpointed)'):
+                chk = Checkpointing(function, Batch(leaves))
+                out_batch = chk.checkpoint()
+                chk.recompute(out_batch)
+                produced = tuple(out_batch)
+        else:
+            with nvtx.annotate(f'fwd mb{mb} stage{self.rank}'):
+                produced = function(leaves)
+
+        if t0 is not None:
+            self._marks.append(('fwd', t0, t1, self._mark()))
+        outs = produced[:flight.n_outputs]
+        stashes = produced[flight.n_outputs:]
+        flight.outputs = produced
+        self._flights[mb] = flight
+        self._outputs[mb] = outs[0] if flight.atomic else outs
+
+        if not self.is_last:
+            tp.send(self.rank + 1, ('fwd', mb, 0),
+                    outs[0].detach() if flight.atomic else tuple(y.detach() for y in outs))
+        for (slot, dst, _), t in zip(self._routes_out, stashes):
+            tp.send(dst, ('skip', mb, slot), t.detach())
 
     @staticmethod
     def _as_leaf(t: Tensor, grad_mode: bool) -> Tensor:
@@ -500,8 +516,9 @@ class DistributedGPipe:
         tp = self.transport
         if losses is not None or output_grads is not None:
             assert self.is_last, 'only the last stage takes losses'
-        for staged in self._graphed.values():
-            staged.refresh_derived_weights()     # once per step, outside the graphs
+        with self.device_lock:
+            for staged in self._graphed.values():
+                staged.refresh_derived_weights()     # once per step, outside the graphs
 
         for mb in reversed(range(self._live)):
             flight = self._flights[mb]
@@ -597,7 +614,6 @@ class DistributedGPipe:
             received = tp.recv(self.rank + 1, ('bwd', mb, 0),
                                like=outs[0] if flight.atomic else outs)
             self._count_bytes(received)
-            received = to(self.device, received)
             gouts.extend((received,) if torch.is_tensor(received) else received)
         for (slot, dst, _), t in zip(self._routes_out, stashes):
             if not t.is_floating_point():
@@ -605,22 +621,24 @@ class DistributedGPipe:
                 continue
             g = tp.recv(dst, ('skip_grad', mb, slot), like=t)
             self._count_bytes(g)
-            gouts.append(to(self.device, g))
-        t1 = self._mark()
+            gouts.append(g)
 
-        with nvtx.annotate(f'bwd mb{mb} stage{self.rank}'):
-            gin = flight.staged.backward(flight.leaves, flight.rng, gouts)
-        if t0 is not None:
-            self._marks.append(('bwd', t0, t1, self._mark()))
+        with self.device_lock:          # every message is here: nothing below waits for a peer
+            gouts = [None if g is None else to(self.device, g) for g in gouts]
+            t1 = self._mark()
+            with nvtx.annotate(f'bwd mb{mb} stage{self.rank}'):
+                gin = flight.staged.backward(flight.leaves, flight.rng, gouts)
+            if t0 is not None:
+                self._marks.append(('bwd', t0, t1, self._mark()))
 
-        leaves = flight.leaves
-        nb = flight.n_boundary
-        if not self.is_first:
-            grads = tuple(self._like_leaf(x, g) for x, g in zip(leaves[:nb], gin[:nb]))
-            tp.send(self.rank - 1, ('bwd', mb, 0), grads[0] if flight.atomic_in else grads)
-        for (slot, src, _), x, g in zip(self._routes_in, leaves[nb:], gin[nb:]):
-            if x.is_floating_point():
-                tp.send(src, ('skip_grad', mb, slot), self._like_leaf(x, g))
+            leaves = flight.leaves
+            nb = flight.n_boundary
+            if not self.is_first:
+                grads = tuple(self._like_leaf(x, g) for x, g in zip(leaves[:nb], gin[:nb]))
+                tp.send(self.rank - 1, ('bwd', mb, 0), grads[0] if flight.atomic_in else grads)
+            for (slot, src, _), x, g in zip(self._routes_in, leaves[nb:], gin[nb:]):
+                if x.is_floating_point():
+                    tp.send(src, ('skip_grad', mb, slot), self._like_leaf(x, g))
 
     @staticmethod
     def _like_leaf(leaf: Tensor, grad: Optional[Tensor]) -> Tensor:

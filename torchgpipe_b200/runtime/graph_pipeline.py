@@ -141,6 +141,13 @@ class GraphedPipeline:
                              checkpoint=checkpoint, cuda_graphs=True, partitions=list(partitions),
                              transport=_Mailboxes(r, self._boxes, self._lock, self._failed))
             for r in range(n)]
+        # Stages that share a device (repeated entries in ``devices``) take turns: a graph capture
+        # on a device must not overlap with work another thread enqueues on that device's
+        # default stream (the capture would be invalidated), so there is one lock per device.
+        locks: Dict[torch.device, Any] = {}
+        for r, stage in enumerate(self.stages):
+            if self.devices.count(self.devices[r]) > 1:
+                stage.device_lock = locks.setdefault(self.devices[r], threading.RLock())
         # a single stage needs no thread: the caller's thread drives it
         self._threads = [_StageThread(r, self.devices[r]) for r in range(n)] if n > 1 else []
         self._anchor = torch.zeros((), device=self.devices[-1], requires_grad=True)

@@ -87,6 +87,7 @@ class GraphedStage:
         self.params = [p for p in module.parameters() if p.requires_grad]
         self._captured: Dict[Signature, _Captured] = {}
         self._pool = None
+        self._capture_stream: Optional[torch.cuda.Stream] = None
         self._derived = [m for m in module.modules() if hasattr(m, 'refresh_derived_weights')]
         # Buffers the forward graph updates in place (BatchNorm running statistics): the
         # recomputation replay must not apply those updates a second time.
@@ -139,9 +140,19 @@ class GraphedStage:
                 self._pool = torch.cuda.graph_pool_handle()
 
             before = ops.launch_count()
-            # thread_local: other threads of this process (the stages of a single-process
-            # pipeline on other devices) keep allocating and launching while this one records
-            with torch.cuda.graph(cap.fwd, pool=self._pool, capture_error_mode='thread_local'):
+            # relaxed: the stages of a single-process pipeline are threads that keep allocating,
+            # freeing and querying events on their own devices while this one records, and this
+            # thread may drop its last reference to a tensor that lives on a neighbour's device
+            # (which makes that device's allocator record / query events) - calls the stricter
+            # capture modes refuse. Work that truly cannot be captured (a host sync on the
+            # capturing stream) still fails in this mode.
+            # The capture stream must belong to this stage's device: torch's default capture
+            # stream is one per process, created on whichever device captured first, and with
+            # it a stage on another device records nothing (its kernels run eagerly, once).
+            if self._capture_stream is None:
+                self._capture_stream = torch.cuda.Stream(self.device)
+            with torch.cuda.graph(cap.fwd, pool=self._pool, stream=self._capture_stream,
+                                  capture_error_mode='relaxed'):
                 with torch.set_grad_enabled(grad):
                     cap.static_outputs = tuple(self.function(tuple(cap.static_inputs)))
             cap.native_launches_fwd = ops.launch_count() - before
@@ -152,8 +163,8 @@ class GraphedStage:
                     (diff_inputs or self.params):
                 cap.bwd = torch.cuda.CUDAGraph()
                 before = ops.launch_count()
-                with torch.cuda.graph(cap.bwd, pool=self._pool,
-                                      capture_error_mode='thread_local'):
+                with torch.cuda.graph(cap.bwd, pool=self._pool, stream=self._capture_stream,
+                                      capture_error_mode='relaxed'):
                     grads = run_backward(cap.static_outputs, cap.static_grad_outputs)
                 cap.native_launches_bwd = ops.launch_count() - before
                 n_in = len(diff_inputs)
