@@ -6,8 +6,11 @@
 For every size prints one JSON line (rank 0): time (CUDA events, max over ranks), achieved
 bytes/s per direction per GPU and the fraction of the roofline
 ``max(flops / peak, wire_bytes / 770 GB/s)`` - the add+scale is 2 flops per element, so the
-link term always dominates. Wire bytes per direction per GPU: P2P two-shot 2N(R-1)/R,
-multicast (NVLS) 2N/R, NCCL ring 2N(R-1)/R.
+link term always dominates. Wire bytes per direction per GPU: P2P 2N(R-1)/R (pulls in, pushes
+out, and the same again for the peers' traffic), NCCL ring 2N(R-1)/R, multicast (NVLS)
+N(R+1)/R: every GPU's whole bucket goes up to the switch once for the in-switch reduction (N
+outbound), the reduced slice comes back (N/R inbound) and the multicast store delivers all R
+slices to every GPU (N inbound).
 """
 import argparse
 import json
@@ -19,7 +22,19 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
 
-LINK_GBS = 770.0        # measured peer-copy bandwidth per direction (B200_PROFILING.md)
+def link_gbs() -> float:
+    """Peer-copy bandwidth per direction: the committed measurement of
+    ``benchmarks/p2p_bandwidth.py`` (``profiles/p2p_bandwidth.json``) when present, else 770."""
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'profiles',
+                        'p2p_bandwidth.json')
+    try:
+        with open(path) as f:
+            return float(json.load(f)['unidirectional_gbs'])
+    except (OSError, ValueError, KeyError):
+        return 770.0
+
+
+LINK_GBS = link_gbs()
 
 
 def timed(fn, iters, device, world):
@@ -63,10 +78,15 @@ def main():
         ms = timed(lambda: fused_allreduce_(buf, 1.0 / world, multicast=False), args.iters,
                    device, world)
         rows.append(('fused_p2p', ms, 2 * nbytes * (world - 1) / world))
+        os.environ['TGB_ALLREDUCE_PULL'] = '1'      # the earlier pull-only two-phase variant
+        ms = timed(lambda: fused_allreduce_(buf, 1.0 / world, multicast=False), args.iters,
+                   device, world)
+        os.environ['TGB_ALLREDUCE_PULL'] = '0'
+        rows.append(('fused_p2p_pull_only', ms, 2 * nbytes * (world - 1) / world))
         if buf.has_multicast:
             ms = timed(lambda: fused_allreduce_(buf, 1.0 / world, multicast=True), args.iters,
                        device, world)
-            rows.append(('fused_nvls', ms, 2 * nbytes / world))
+            rows.append(('fused_nvls', ms, nbytes * (world + 1) / world))
         assert int(buf.error_flag.item()) == 0
         if dist.get_rank() == 0:
             for name, ms, wire in rows:
@@ -74,7 +94,7 @@ def main():
                 print(json.dumps({'op': name, 'mib': mib, 'replicas': world, 'ms': round(ms, 4),
                                   'wire_gbs_per_dir': round(wire / ms / 1e6, 1),
                                   'algbw_gbs': round(nbytes / ms / 1e6, 1),
-                                  'roofline_ms': round(ideal_ms, 4),
+                                  'roofline_ms': round(ideal_ms, 4), 'link_gbs': LINK_GBS,
                                   'fraction_of_roofline': round(ideal_ms / ms, 3)}), flush=True)
         del buf
     dist.barrier()

@@ -6,18 +6,25 @@
 // multicast address that targets all replicas at once (NVLS). One kernel does everything:
 //
 //   barrier            all replicas have finished writing their gradients
-//   reduce-scatter     rank r sums slice r of all replicas
+//   reduce + scatter   rank r sums slice r of all replicas
 //                        P2P     : ld.global from each peer's bucket
 //                        NVLS    : multimem.ld_reduce.add (the switch adds, one load returns the sum)
-//                      multiplies by `scale` (1 / replicas, loss scale, ...) - the fused part
-//   all-gather           P2P     : writes the finished slice into every replica's bucket
+//                      multiplies by `scale` (1 / replicas, loss scale, ...) - the fused part -
+//                      and hands the finished values out in the same pass:
+//                        P2P     : st.global into slice r of every replica's bucket (push)
 //                        NVLS    : multimem.st (the switch replicates the store)
 //                      and optionally writes a bf16 copy locally
 //   barrier            every replica holds the full reduced bucket; buffers may be reused
 //
-// In place and race free: in the reduce phase slice r of any bucket is only read; it is written
-// (by rank r alone) only after the middle barrier. Bytes on the wire per direction per GPU:
-// P2P 2N(R-1)/R, NVLS about 2N/R - the roofline bench.py/benchmarks report against.
+// In place and race free without a barrier in the middle: element e of slice r is read - in any
+// bucket - by rank r alone, and by exactly the thread that then overwrites it everywhere, after
+// its loads have returned. Loads (inbound) and stores (outbound) keep both directions of the
+// links busy at once, and posted stores do not pay the NVLink round trip. Bytes on the wire per
+// direction per GPU: P2P 2N(R-1)/R; NVLS N(R+1)/R (the whole bucket goes up to the switch once
+// for the in-switch reduction, every reduced slice comes down to every GPU once) - the roofline
+// the benchmarks report against. NVLS therefore wins from three replicas up, P2P at two.
+// (The earlier pull-only version - reduce, barrier, then every rank pulls the finished slices -
+// is kept behind TGB_ALLREDUCE_PULL=1 for A/B timing.)
 //
 // Cross-GPU barriers use a per-rank signal pad (a second, zero-initialised symmetric allocation
 // owned by the caller, tgb_allreduce_pad_bytes() bytes): block b of rank r
@@ -30,6 +37,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <cstdlib>
 #include "tgb_internal.h"
 
 namespace tgb {
@@ -107,7 +115,7 @@ __device__ __forceinline__ void multimem_st_f4(float* p, float4 v) {
                : "memory");
 }
 
-template <bool NVLS>
+template <bool NVLS, bool PUSH>
 __global__ void __launch_bounds__(kArThreads, 1) allreduce_scale_kernel(const ArParams p) {
   if (!replica_barrier(p, p.ticket + 1)) return;
 
@@ -141,10 +149,16 @@ __global__ void __launch_bounds__(kArThreads, 1) allreduce_scale_kernel(const Ar
       // slice r of any bucket during the reduce phase except rank r itself
       multimem_st_f4(p.mc + e, acc);
     } else {
-      // slice r of the LOCAL bucket is read by this thread only (peers read their own slice
-      // index of this bucket), so it can be overwritten right away; peers fetch it after the
-      // middle barrier
+      // slice r of ANY bucket is read by this thread only (peers read their own slice index),
+      // so it can be overwritten right away, here and - PUSH - in every peer's bucket
       st_f4(mine + e, acc);
+      if (PUSH) {
+#pragma unroll
+        for (int k = 1; k < kArMaxWorld; ++k) {
+          if (k >= p.world) break;
+          st_f4(p.bufs[(p.rank + k) % p.world] + e, acc);
+        }
+      }
     }
     if (p.cast_out != nullptr) {
       __nv_bfloat162 lo = __floats2bfloat162_rn(acc.x, acc.y);
@@ -156,8 +170,8 @@ __global__ void __launch_bounds__(kArThreads, 1) allreduce_scale_kernel(const Ar
 
   if (!replica_barrier(p, p.ticket + 2)) return;
 
-  // ---- all-gather: fetch the other ranks' finished slices (P2P); NVLS already multicast them
-  if (!NVLS) {
+  // ---- pull variant: fetch the other ranks' finished slices; NVLS / PUSH already delivered them
+  if (!NVLS && !PUSH) {
     for (int k = 1; k < p.world; ++k) {
       const int peer = (p.rank + k) % p.world;
       const unsigned long long pb = slice * peer;
@@ -177,7 +191,8 @@ __global__ void __launch_bounds__(kArThreads, 1) allreduce_scale_kernel(const Ar
       }
     }
   } else if (p.cast_out != nullptr) {
-    // bf16 copy of the slices other ranks produced (they are now in the local bucket)
+    // bf16 copy of the slices other ranks produced (they are in the local bucket now: the
+    // barrier above was passed by every replica after its last store)
     for (int k = 1; k < p.world; ++k) {
       const unsigned long long pb = slice * ((p.rank + k) % p.world);
       for (unsigned long long i =
@@ -192,7 +207,8 @@ __global__ void __launch_bounds__(kArThreads, 1) allreduce_scale_kernel(const Ar
     }
   }
 
-  replica_barrier(p, p.ticket + 3);
+  // pull variant only: peers are still reading this rank's slice until they pass this point
+  if (!NVLS && !PUSH) replica_barrier(p, p.ticket + 3);
 }
 
 }  // namespace tgb
@@ -243,10 +259,14 @@ extern "C" int tgb_allreduce_scale_f32(void* const* bufs, void* const* pads, voi
   const unsigned long long vecs = n / world / 4;
   const unsigned long long want = (vecs + kArThreads - 1) / kArThreads;
   if (want < static_cast<unsigned long long>(blocks)) blocks = static_cast<int>(want ? want : 1);
+  const char* pull_env = getenv("TGB_ALLREDUCE_PULL");         // read per call: A/B in one run
+  const bool pull = pull_env != nullptr && pull_env[0] == '1';
   if (multicast != nullptr)
-    allreduce_scale_kernel<true><<<blocks, kArThreads, 0, stream>>>(p);
+    allreduce_scale_kernel<true, false><<<blocks, kArThreads, 0, stream>>>(p);
+  else if (pull)
+    allreduce_scale_kernel<false, false><<<blocks, kArThreads, 0, stream>>>(p);
   else
-    allreduce_scale_kernel<false><<<blocks, kArThreads, 0, stream>>>(p);
+    allreduce_scale_kernel<false, true><<<blocks, kArThreads, 0, stream>>>(p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return set_error("allreduce launch: %s", cudaGetErrorString(e));
   count_launch();

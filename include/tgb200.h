@@ -270,7 +270,7 @@ int tgb_bn_add_act_bwd(const float* dz, const float* y, const float* z, const fl
  *   launch_index : same on every rank, +1 per call on these buffers (derives barrier tickets)
  *   error_flag : device int set to 1 if a peer did not arrive within timeout_ms
  * All replicas must launch the call; it must not be wrapped with other kernels that wait on a
- * peer. Wire bytes per direction per GPU: P2P 2N(R-1)/R, multicast about 2N/R.
+ * peer. Wire bytes per direction per GPU: P2P 2N(R-1)/R, multicast N(R+1)/R.
  * Reference: none - the reference has no data parallelism; NCCL all_reduce on the
  * same bucket is the baseline. */
 int tgb_allreduce_scale_f32(void* const* bufs, void* const* pads, void* multicast,

@@ -68,3 +68,57 @@ def test_fused_allreduce_matches_nccl():
             err, cerr = value
             assert err < 1e-5, (rank, key, err)
             assert cerr < 5e-2, (rank, key, cerr)
+
+
+def _hybrid_worker(rank, world, port, ret):
+    """1 pipeline stage x 2 replicas on 2 GPUs: the fused kernel on the symmetric bucket IS the
+    data-parallel all-reduce (use_symmetric=True), through the CUDA-graph stage engine."""
+    import torch.distributed as dist
+    from torch import nn
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group('nccl', rank=rank, world_size=world)
+    try:
+        from torchgpipe_b200 import ops
+        from torchgpipe_b200.parallel import HybridLayout, HybridPipeline
+        device = torch.device('cuda', rank)
+        torch.manual_seed(0)
+        plain = nn.Sequential(nn.Conv2d(8, 16, 3, padding=1, bias=False), nn.BatchNorm2d(16),
+                              nn.ReLU(), nn.Conv2d(16, 8, 1, bias=False))
+        import copy
+        model = ops.convert_to_sm100(copy.deepcopy(plain))
+        layout = HybridLayout(stages=1, replicas=world)
+        hybrid = HybridPipeline(model, [4], 2, layout, device, checkpoint='except_last',
+                                cuda_graphs=True, use_symmetric=True)
+        assert hybrid.bucket.symmetric is not None
+        x = torch.randn(4, 8, 10, 10, generator=torch.Generator().manual_seed(7 + rank)).to(device)
+        for step in range(2):                   # second step: graphs replay, bucket reused
+            hybrid.zero_grad()
+            outs = hybrid.forward(x)
+            hybrid.backward([o.square().mean() / 2 for o in outs])
+        torch.cuda.synchronize()
+        got = [p.grad.detach().clone().cpu() for p in hybrid.model().parameters()]
+        # oracle: the plain model on this replica's data, gradients averaged with NCCL
+        plain = plain.to(device)
+        loss = sum(plain(c).square().mean() / 2 for c in x.chunk(2))
+        loss.backward()
+        want = []
+        for p in plain.parameters():
+            g = p.grad.detach().clone()
+            dist.all_reduce(g)
+            want.append((g / world).cpu())
+        ret[rank] = [(float((a - b).norm() / b.norm().clamp_min(1e-12))) for a, b in zip(got, want)]
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(240)
+def test_hybrid_pipeline_uses_the_fused_allreduce_on_gpus():
+    world = 2
+    port = 29900 + os.getpid() % 1000
+    ret = mp.Manager().dict()
+    mp.spawn(_hybrid_worker, args=(world, port, ret), nprocs=world, join=True)
+    for rank in range(world):
+        assert all(err < 2e-2 for err in ret[rank]), (rank, ret[rank])
