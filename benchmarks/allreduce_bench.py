@@ -5,7 +5,7 @@
 
 For every size prints one JSON line (rank 0): time (CUDA events, max over ranks), achieved
 bytes/s per direction per GPU and the fraction of the roofline
-``max(flops / peak, wire_bytes / 770 GB/s)`` - the add+scale is 2 flops per element, so the
+``max(flops / peak, wire_bytes / measured link bandwidth)`` - the add+scale is 2 flops per element, so the
 link term always dominates. Wire bytes per direction per GPU: P2P 2N(R-1)/R (pulls in, pushes
 out, and the same again for the peers' traffic), NCCL ring 2N(R-1)/R, multicast (NVLS)
 N(R+1)/R: every GPU's whole bucket goes up to the switch once for the in-switch reduction (N
@@ -22,19 +22,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
 
-def link_gbs() -> float:
-    """Peer-copy bandwidth per direction: the committed measurement of
-    ``benchmarks/p2p_bandwidth.py`` (``profiles/p2p_bandwidth.json``) when present, else 770."""
-    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'profiles',
-                        'p2p_bandwidth.json')
-    try:
-        with open(path) as f:
-            return float(json.load(f)['unidirectional_gbs'])
-    except (OSError, ValueError, KeyError):
-        return 770.0
+from torchgpipe_b200.utils import link_bandwidth_gbs  # noqa: E402
 
-
-LINK_GBS = link_gbs()
+LINK_GBS = link_bandwidth_gbs()      # measured by benchmarks/p2p_bandwidth.py
 
 
 def timed(fn, iters, device, world):

@@ -24,7 +24,9 @@ import torch.distributed as dist
 import torch.nn.functional as F
 from torch.optim import SGD
 
-LINK_GBS = 770.0
+from torchgpipe_b200.utils import link_bandwidth_gbs  # noqa: E402
+
+LINK_GBS = link_bandwidth_gbs()      # measured by benchmarks/p2p_bandwidth.py
 
 
 def even_balance(n_layers, stages):

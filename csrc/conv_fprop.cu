@@ -454,6 +454,324 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
   }
 }
 
+// ---------------------------------------------------------------- CTA-pair variant (BN = 256)
+// Two CTAs of a cluster compute a 256-pixel x 256-channel tile with tcgen05.mma.cta_group::2
+// (M = 256): each CTA loads its own 128-pixel A box and HALF of the B tile (128 of the 256
+// output channels) - per k-block 32 KB of operands per SM instead of 48 KB, which is what the
+// 1-CTA BN=256 kernel is bound by (shared-memory operand reads of the MMA and L2 -> SM fill).
+// The leader (cluster rank 0) issues every MMA; its full barrier is credited by the TMA loads
+// of both CTAs, its tcgen05.commit arrives on the empty / accumulator-ready barriers of both
+// CTAs (multicast), and the epilogue warps of both CTAs release the accumulator stage on the
+// leader's barrier. Every CTA runs its own epilogue on its own 128 TMEM lanes.
+// All tensor maps cover this GPU's memory only; no load is multicast.
+constexpr int kPairBN = 256;
+
+template <int STAGES>
+struct PairSmem {
+  static constexpr int kABytes = kBlockM * kBlockKBytes;              // 16 KB
+  static constexpr int kBBytes = (kPairBN / 2) * kBlockKBytes;        // 16 KB: this CTA's half
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kEpiBytes = kBlockM * kBlockKBytes;
+  static constexpr int kEpiOffset = STAGES * kStageBytes;
+  static constexpr int kStatOffset = kEpiOffset + 2 * kEpiBytes;
+  static constexpr int kBarOffset = kStatOffset + 1536;
+  static constexpr int kTotal = kBarOffset + (2 * STAGES + 4) * 8 + 16;
+};
+
+template <int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+conv_fprop_tf32_pair_kernel(const __grid_constant__ CUtensorMap tmap_x,
+                            const __grid_constant__ CUtensorMap tmap_x1,
+                            const __grid_constant__ CUtensorMap tmap_x2,
+                            const __grid_constant__ CUtensorMap tmap_x3,
+                            const __grid_constant__ CUtensorMap tmap_w,
+                            const __grid_constant__ CUtensorMap tmap_y,
+                            const ConvGeom g, float* __restrict__ stats) {
+  using L = PairSmem<STAGES>;
+  constexpr int BN = kPairBN;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // both CTAs of the pair must use identical offsets: the dynamic shared window starts at the
+  // same address in every CTA of a kernel, so the same round-up applies to both
+  uint8_t* smem = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);   // used in the leader
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full = empty_bar + STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;                                     // used in the leader
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int rows_valid = g.BW * g.BH * g.BNB;
+  const int pix_tiles = g.tiles_w * g.tiles_h * g.tiles_n;
+  const int pair_tiles = (pix_tiles + 1) / 2;
+  const int num_items = pair_tiles * g.tiles_k * g.splits;
+  const int k_iters = g.R * g.S * g.c_blocks;
+  const uint32_t stage_tx = static_cast<uint32_t>(rows_valid * kBlockKBytes + L::kBBytes);
+  const int first_item = static_cast<int>(blockIdx.x >> 1);
+  const int item_stride = static_cast<int>(gridDim.x >> 1);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_w);
+    tma_prefetch_desc(&tmap_y);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);          // the leader's own arrive.expect_tx (bytes of both)
+      mbar_init(&empty_bar[s], 1);         // one multicast commit
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);         // one multicast commit
+      mbar_init(&tmem_empty[s], 8);        // four epilogue warps in each CTA of the pair
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc_pair(tmem_slot, 2 * BN);
+  tc_fence_before();
+  cluster_sync_all();                      // barriers of both CTAs exist before anyone signals
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  int it_begin = 0, it_end = k_iters;
+  bool valid = true;
+  auto decode = [&](int item, int& kt, int& tw, int& th, int& tn) {
+    const int ks = item % g.splits;
+    item /= g.splits;
+    it_begin = ks * g.iters_per_split;
+    it_end = min(k_iters, it_begin + g.iters_per_split);
+    kt = item % g.tiles_k;
+    const int p = 2 * (item / g.tiles_k) + static_cast<int>(rank);    // this CTA's pixel tile
+    valid = p < pix_tiles;
+    if (valid) {
+      tw = p % g.tiles_w;
+      const int rest = p / g.tiles_w;
+      th = rest % g.tiles_h;
+      tn = rest / g.tiles_h;
+    } else {              // odd tile count: the partner of the last tile works on nothing -
+      tw = 0;             // its boxes lie outside the tensor (zero-filled loads, clipped stores)
+      th = 0;
+      tn = g.tiles_n;
+    }
+  };
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer (both CTAs)
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = first_item; item < num_items; item += item_stride) {
+        int kt, tw, th, tn;
+        decode(item, kt, tw, th, tn);
+        const int n0 = tn * g.BNB;
+        const int k0 = kt * BN + static_cast<int>(rank) * (BN / 2);   // this CTA's half of B
+        int tap = it_begin / g.c_blocks;
+        int cb = it_begin - tap * g.c_blocks;
+        for (int it = it_begin; it < it_end; ++it) {
+          const int r = tap / g.S;
+          const int s = tap - r * g.S;
+          const int ar = r - g.pad_h, as = s - g.pad_w;
+          const int qr = floor_div(ar, g.stride_h), qs = floor_div(as, g.stride_w);
+          const int view = (ar - qr * g.stride_h) * g.stride_w + (as - qs * g.stride_w);
+          const CUtensorMap* mx = view == 0 ? &tmap_x : view == 1 ? &tmap_x1
+                                : view == 2 ? &tmap_x2 : &tmap_x3;
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* a_dst = smem + stage * L::kStageBytes;
+          uint8_t* b_dst = a_dst + L::kABytes;
+          if (leader) mbar_expect_tx(&full_bar[stage], 2 * stage_tx);
+          const uint32_t bar = mapa_u32(&full_bar[stage], 0);         // the leader's barrier
+          tma_load_4d_pair(a_dst, mx, bar, cb * kBlockK, tw * g.BW + qs, th * g.BH + qr, n0);
+          tma_load_4d_pair(b_dst, &tmap_w, bar, cb * kBlockK, tap, k0, 0);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+          if (++cb == g.c_blocks) {
+            cb = 0;
+            ++tap;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (leader only)
+    constexpr uint32_t idesc = make_idesc(/*tf32*/ 2, 2 * kBlockM, BN, 0, 0);
+    if (leader && elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int item = first_item; item < num_items; item += item_stride) {
+        int kt_, tw_, th_, tn_;
+        decode(item, kt_, tw_, th_, tn_);
+        const int n_it = it_end - it_begin;
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int it = 0; it < n_it; ++it) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
+          const uint64_t a_desc = make_smem_desc_sw128(a_addr, 16, 1024);
+          const uint64_t b_desc = make_smem_desc_sw128(a_addr + L::kABytes, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k)
+            mma_tf32_ss_pair(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc,
+                             (it > 0 || k > 0) ? 1u : 0u);
+          mma_commit_pair(&empty_bar[stage], 0b11);
+          if (it == n_it - 1) mma_commit_pair(&tmem_full[acc], 0b11);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------ epilogue (both CTAs)
+    const int q = warp - 4;
+    const int row = q * 32 + lane;
+    const int epi_tid = threadIdx.x - 128;
+    uint8_t* epi = smem + L::kEpiOffset;
+    float2* stat_part = reinterpret_cast<float2*>(smem + L::kStatOffset);
+    int* row_img = reinterpret_cast<int*>(smem + L::kStatOffset + 1024);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    int chunk_counter = 0;
+    for (int item = first_item; item < num_items; item += item_stride) {
+      int kt, tw, th, tn;
+      decode(item, kt, tw, th, tn);
+      bool tile_uniform = false;
+      if (g.stats_mode != 0) {
+        tile_uniform = valid && g.BNB == 1 && (tw + 1) * g.BW <= g.Wo &&
+                       (th + 1) * g.BH <= g.Ho;
+        if (!tile_uniform) {
+          asm volatile("bar.sync 2, 128;" ::: "memory");
+          const int ww = row % g.BW;
+          const int hh = (row / g.BW) % g.BH;
+          const int nn = row / (g.BW * g.BH);
+          const bool inside = valid && row < rows_valid && tw * g.BW + ww < g.Wo &&
+                              th * g.BH + hh < g.Ho && tn * g.BNB + nn < g.N;
+          row_img[row] = inside ? (g.stats_mode == 1 ? tn * g.BNB + nn : 0) : -1;
+        }
+      }
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+#pragma unroll 1
+      for (int j = 0; j < BN / kEpiChunk; ++j, ++chunk_counter) {
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + static_cast<uint32_t>(acc * BN + j * kEpiChunk) +
+                               (static_cast<uint32_t>(q * 32) << 16);
+        tmem_ld_32x32(taddr, v);
+        tmem_ld_wait();
+        if (j == BN / kEpiChunk - 1) {
+          // accumulator fully read: release the TMEM stage on the LEADER's barrier
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_u32(&tmem_empty[acc], 0));
+        }
+        uint8_t* buf = epi + (chunk_counter & 1) * L::kEpiBytes;
+        if (epi_tid == 0) tma_store_wait_read<1>();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        {
+          uint8_t* rowp = buf + row * kBlockKBytes;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const int pc = c ^ (row & 7);
+            *reinterpret_cast<uint4*>(rowp + pc * 16) =
+                make_uint4(v[4 * c + 0], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+          }
+        }
+        fence_proxy_async_smem();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (epi_tid == 0) {
+          if (g.splits > 1)
+            tma_reduce_add_4d(&tmap_y, buf, kt * BN + j * kEpiChunk, tw * g.BW, th * g.BH,
+                              tn * g.BNB);
+          else
+            tma_store_4d(&tmap_y, buf, kt * BN + j * kEpiChunk, tw * g.BW, th * g.BH,
+                         tn * g.BNB);
+          tma_store_commit();
+        }
+        if (g.stats_mode != 0) {
+          const int col = lane;
+          const int kglob = kt * BN + j * kEpiChunk + col;
+          const int sw_hi = col >> 2, sw_lo = (col & 3) * 4;
+          if (tile_uniform) {
+            float s1 = 0.f, s2 = 0.f;
+            const int r_end = min(32, rows_valid - q * 32);
+#pragma unroll 8
+            for (int rr = 0; rr < r_end; ++rr) {
+              const int r2 = q * 32 + rr;
+              const float x = *reinterpret_cast<const float*>(
+                  buf + r2 * kBlockKBytes + ((sw_hi ^ (r2 & 7)) << 4) + sw_lo);
+              s1 += x;
+              s2 = fmaf(x, x, s2);
+            }
+            stat_part[q * 32 + col] = make_float2(s1, s2);
+            asm volatile("bar.sync 2, 128;" ::: "memory");
+            if (q == 0 && kglob < g.K) {
+              const float2 p0 = stat_part[col], p1 = stat_part[32 + col];
+              const float2 p2 = stat_part[64 + col], p3 = stat_part[96 + col];
+              const int img = (g.stats_mode == 1) ? tn : 0;
+              float* dst = stats + (static_cast<size_t>(img) * g.K + kglob) * 2;
+              atomicAdd(dst, (p0.x + p1.x) + (p2.x + p3.x));
+              atomicAdd(dst + 1, (p0.y + p1.y) + (p2.y + p3.y));
+            }
+          } else {
+            float s1 = 0.f, s2 = 0.f;
+            int cur_img = -1;
+            for (int rr = 0; rr < 32; ++rr) {
+              const int r2 = q * 32 + rr;
+              if (r2 >= rows_valid) break;
+              const int img = row_img[r2];
+              if (img < 0) continue;
+              if (img != cur_img) {
+                if (cur_img >= 0 && kglob < g.K) {
+                  float* dst = stats + (static_cast<size_t>(cur_img) * g.K + kglob) * 2;
+                  atomicAdd(dst, s1);
+                  atomicAdd(dst + 1, s2);
+                }
+                cur_img = img;
+                s1 = 0.f;
+                s2 = 0.f;
+              }
+              const float x = *reinterpret_cast<const float*>(
+                  buf + r2 * kBlockKBytes + ((sw_hi ^ (r2 & 7)) << 4) + sw_lo);
+              s1 += x;
+              s2 = fmaf(x, x, s2);
+            }
+            if (cur_img >= 0 && kglob < g.K) {
+              float* dst = stats + (static_cast<size_t>(cur_img) * g.K + kglob) * 2;
+              atomicAdd(dst, s1);
+              atomicAdd(dst + 1, s2);
+            }
+          }
+        }
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+    if (epi_tid == 0) tma_store_wait_all<0>();
+  }
+
+  tc_fence_before();
+  cluster_sync_all();                      // nobody leaves while the partner may still signal
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, 2 * BN);
+  }
+}
+
 // ---------------------------------------------------------------- host side
 static void choose_pixel_box(int N, int Ho, int Wo, int stats_mode, int& BW, int& BH, int& BNB) {
   // Largest-utilisation box with BW*BH*BNB <= 128 that wastes the fewest rows on partial tiles.
@@ -517,6 +835,47 @@ static int launch_fprop(const XMaps& mx, const CUtensorMap& mw, const CUtensorMa
   if (e != cudaSuccess) return set_error("conv_fprop launch: %s", cudaGetErrorString(e));
   count_launch();
   return 0;
+}
+
+template <int STAGES>
+static int launch_fprop_pair(const XMaps& mx, const CUtensorMap& mw, const CUtensorMap& my,
+                             const ConvGeom& g, float* stats, int sm_count, cudaStream_t stream) {
+  using L = PairSmem<STAGES>;
+  constexpr int smem_bytes = L::kTotal + 1024;
+  static bool configured_on[64] = {false};
+  int dev_ = 0;
+  cudaGetDevice(&dev_);
+  if (dev_ < 0 || dev_ >= 64) dev_ = 0;
+  bool& configured = configured_on[dev_];
+  auto kern = conv_fprop_tf32_pair_kernel<STAGES>;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         smem_bytes);
+    if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(conv_fprop_pair): %s",
+                                           cudaGetErrorString(e));
+    configured = true;
+  }
+  const int pix_tiles = g.tiles_w * g.tiles_h * g.tiles_n;
+  const int items = (pix_tiles + 1) / 2 * g.tiles_k * g.splits;
+  const int pairs = sm_count / 2;
+  const int grid = 2 * (items < pairs ? items : pairs);
+  kern<<<grid, kThreads, smem_bytes, stream>>>(mx.m[0], mx.m[1], mx.m[2], mx.m[3], mw, my, g,
+                                               stats);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_error("conv_fprop_pair launch: %s", cudaGetErrorString(e));
+  count_launch();
+  return 0;
+}
+
+// CTA pairs for BN = 256 tiles (default on; TGB_FPROP_2CTA=0 falls back to one CTA per tile).
+// Measured on B200, U-Net layers at micro-batch 40 (build/selftest, TFLOP/s TF32, 1 CTA -> pair):
+// 2048->2048 @6x6 714 -> 784, 1024->1024 @12x12 753 -> 770, 512->512 @24x24 711 -> 728,
+// 256->256 @48x48 789 -> 792 (the last one already sits at the TF32 roof of about 800).
+static bool use_cta_pairs(int BN, bool halo, const ConvGeom& g) {
+  if (BN != kPairBN || halo) return false;
+  if (g.tiles_w * g.tiles_h * g.tiles_n < 2) return false;
+  const char* env = getenv("TGB_FPROP_2CTA");
+  return env != nullptr ? atoi(env) != 0 : true;
 }
 
 // Everything that is decided on the host before a launch: tile shapes, kernel variant, split of
@@ -634,14 +993,27 @@ struct ConvProblem {
   int stats_mode;
 };
 
-static int run_fprop(const ConvProblem& p, cudaStream_t stream) {
-  if (p.C % 4 != 0 || p.K % 4 != 0)
-    return set_error("conv_fprop: need C %% 4 == 0 and K %% 4 == 0 (got C=%d K=%d)", p.C, p.K);
-  if ((reinterpret_cast<uintptr_t>(p.x) | reinterpret_cast<uintptr_t>(p.w) |
-       reinterpret_cast<uintptr_t>(p.y)) & 15)
+static int run_fprop(const ConvProblem& p_in, cudaStream_t stream) {
+  if (p_in.C % 4 != 0 || p_in.K % 4 != 0)
+    return set_error("conv_fprop: need C %% 4 == 0 and K %% 4 == 0 (got C=%d K=%d)", p_in.C,
+                     p_in.K);
+  if ((reinterpret_cast<uintptr_t>(p_in.x) | reinterpret_cast<uintptr_t>(p_in.w) |
+       reinterpret_cast<uintptr_t>(p_in.y)) & 15)
     return set_error("conv_fprop: tensors must be 16-byte aligned");
-  if ((p.x_sw | p.x_sh | p.x_sn | p.y_sw | p.y_sh | p.y_sn) & 3)
+  if ((p_in.x_sw | p_in.x_sh | p_in.x_sn | p_in.y_sw | p_in.y_sh | p_in.y_sn) & 3)
     return set_error("conv_fprop: strides must be multiples of 4 elements (16 bytes)");
+  // stats_mode < 0: same as -stats_mode, and the accumulators are zeroed here first (a memset
+  // on the stream instead of a fill kernel issued by the caller)
+  ConvProblem q = p_in;
+  if (q.stats_mode < 0) {
+    q.stats_mode = -q.stats_mode;
+    if (q.stats != nullptr) {
+      const size_t n = (q.stats_mode == 1 ? static_cast<size_t>(q.N) : 1) * q.K * 2 * 4;
+      cudaError_t e = cudaMemsetAsync(q.stats, 0, n, stream);
+      if (e != cudaSuccess) return set_error("conv_fprop: memset(stats): %s", cudaGetErrorString(e));
+    }
+  }
+  const ConvProblem& p = q;
   ConvGeom g;
   int BN = 32;
   bool halo = false, resident = false;
@@ -666,6 +1038,7 @@ static int run_fprop(const ConvProblem& p, cudaStream_t stream) {
 
   XMaps mx;
   CUtensorMap mw, my;
+  const bool pairs = use_cta_pairs(BN, halo, g);
   const int views = p.stride_h * p.stride_w;
   for (int v = 0; v < 4; ++v) {
     // view (ph, pw): the pixels with h = stride_h*hh + ph, w = stride_w*ww + pw. Views past
@@ -694,7 +1067,8 @@ static int run_fprop(const ConvProblem& p, cudaStream_t stream) {
     uint64_t dims[4] = {(uint64_t)p.C, (uint64_t)(p.R * p.S), (uint64_t)p.K, 1};
     uint64_t strides[3] = {(uint64_t)p.C * 4, (uint64_t)p.R * p.S * p.C * 4,
                            (uint64_t)p.K * p.R * p.S * p.C * 4};
-    uint32_t box[4] = {32, 1, (uint32_t)BN, 1};
+    // a CTA pair loads the B tile in two halves, one per CTA
+    uint32_t box[4] = {32, 1, (uint32_t)(pairs ? BN / 2 : BN), 1};
     if (make_tensor_map(&mw, p.w, 4, 4, dims, strides, box, 1))
       return set_error("conv_fprop: tensor map for W failed");
   }
@@ -706,7 +1080,9 @@ static int run_fprop(const ConvProblem& p, cudaStream_t stream) {
       return set_error("conv_fprop: tensor map for Y failed");
   }
   int rc;
-  if (halo && resident) {
+  if (pairs) {
+    rc = launch_fprop_pair<5>(mx, mw, my, g, p.stats, sms, stream);
+  } else if (halo && resident) {
     rc = BN == 64 ? launch_fprop<64, 2, true, true>(mx, mw, my, g, p.stats, sms, stream)
                   : launch_fprop<32, 2, true, true>(mx, mw, my, g, p.stats, sms, stream);
   } else if (halo) {

@@ -88,14 +88,18 @@ moments_kernel(const float* __restrict__ a, const float* __restrict__ b,
 
 // ------------------------------------------------------------------ InstanceNorm cell
 // coef[g][c] = ms / sqrt(ms^2 * var + eps), mean[g][c]; ms = dropout scale (0 or 1/(1-p)).
+// drop_p > 0: `ms` holds uniform random numbers in [0,1) and the Dropout2d mask is made here
+// (channel kept when u >= p, scaled by 1/(1-p)) instead of by separate compare / scale kernels.
 __global__ void in_prepare_kernel(const float* __restrict__ stats, const float* __restrict__ ms,
-                                  float* __restrict__ mean_coef, int GC, float inv_p, float eps) {
+                                  float* __restrict__ mean_coef, int GC, float inv_p, float eps,
+                                  float drop_p) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= GC) return;
   const float s1 = stats[2 * i], s2 = stats[2 * i + 1];
   const float mu = s1 * inv_p;
   const float var = fmaxf(s2 * inv_p - mu * mu, 0.f);
-  const float m = ms ? ms[i] : 1.f;
+  float m = ms ? ms[i] : 1.f;
+  if (ms && drop_p > 0.f) m = m >= drop_p ? 1.f / (1.f - drop_p) : 0.f;
   mean_coef[2 * i] = mu;
   mean_coef[2 * i + 1] = m * rsqrtf(m * m * var + eps);
 }
@@ -164,13 +168,22 @@ in_backward_kernel(const float* __restrict__ dz, const float* __restrict__ z,
 // y_norm = y * a + b, a = gamma * rstd, b = beta - mean * a; saved[c] = (mean, rstd) for backward.
 // Optionally folds the batch statistics into the running estimates exactly like nn.BatchNorm2d
 // (unbiased variance for running_var, momentum < 0 selects the cumulative average 1/count).
+// `tracked` (optional): nn.BatchNorm2d's num_batches_tracked. With it the kernel runs as ONE
+// block: every thread reads the old count, then thread 0 adds one - the counter update costs no
+// launch of its own, and momentum < 0 (cumulative average) uses 1/(count+1) without a host read.
 __global__ void bn_prepare_kernel(const float* __restrict__ stats, const float* __restrict__ gamma,
                                   const float* __restrict__ beta, float* __restrict__ coef,
                                   float* __restrict__ saved, float* __restrict__ running_mean,
                                   float* __restrict__ running_var, int C, float inv_p,
-                                  float unbias, float eps, float momentum) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+                                  float unbias, float eps, float momentum,
+                                  long long* __restrict__ tracked) {
+  if (tracked != nullptr) {
+    const long long count = *tracked + 1;
+    if (momentum < 0.f) momentum = 1.f / static_cast<float>(count);
+    __syncthreads();
+    if (threadIdx.x == 0) *tracked = count;
+  }
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < C; c += gridDim.x * blockDim.x) {
   const float mu = stats[2 * c] * inv_p;
   const float var = fmaxf(stats[2 * c + 1] * inv_p - mu * mu, 0.f);
   const float rstd = rsqrtf(var + eps);
@@ -183,6 +196,7 @@ __global__ void bn_prepare_kernel(const float* __restrict__ stats, const float* 
   if (running_mean != nullptr) {
     running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mu;
     running_var[c] = (1.f - momentum) * running_var[c] + momentum * var * unbias;
+  }
   }
 }
 
@@ -284,8 +298,20 @@ extern "C" int tgb_in_prepare(const float* stats, const float* drop_scale, float
                               int G, int P, int C, float eps, cudaStream_t stream) {
   const int gc = G * C;
   in_prepare_kernel<<<(gc + 255) / 256, 256, 0, stream>>>(stats, drop_scale, mean_coef, gc,
-                                                          1.f / static_cast<float>(P), eps);
+                                                          1.f / static_cast<float>(P), eps, 0.f);
   TGB_CHECK_LAUNCH("in_prepare");
+  return 0;
+}
+
+extern "C" int tgb_in_prepare_dropout(const float* stats, const float* uniform, float drop_p,
+                                      float* mean_coef, int G, int P, int C, float eps,
+                                      cudaStream_t stream) {
+  if (!(drop_p >= 0.f && drop_p < 1.f)) return set_error("in_prepare_dropout: p must be in [0,1)");
+  const int gc = G * C;
+  in_prepare_kernel<<<(gc + 255) / 256, 256, 0, stream>>>(
+      stats, drop_p > 0.f ? uniform : nullptr, mean_coef, gc, 1.f / static_cast<float>(P), eps,
+      drop_p);
+  TGB_CHECK_LAUNCH("in_prepare_dropout");
   return 0;
 }
 
@@ -322,8 +348,22 @@ extern "C" int tgb_bn_prepare(const float* stats, const float* gamma, const floa
   bn_prepare_kernel<<<(C + 255) / 256, 256, 0, stream>>>(stats, gamma, beta, coef, saved,
                                                         running_mean, running_var, C,
                                                         1.f / static_cast<float>(P), unbias, eps,
-                                                        momentum);
+                                                        momentum, nullptr);
   TGB_CHECK_LAUNCH("bn_prepare");
+  return 0;
+}
+
+extern "C" int tgb_bn_prepare_tracked(const float* stats, const float* gamma, const float* beta,
+                                      float* coef, float* saved, float* running_mean,
+                                      float* running_var, long long* num_batches_tracked, int P,
+                                      int C, float eps, float momentum, cudaStream_t stream) {
+  const float unbias = P > 1 ? static_cast<float>(P) / static_cast<float>(P - 1) : 1.f;
+  if (num_batches_tracked == nullptr && momentum < 0.f)
+    return set_error("bn_prepare_tracked: the cumulative average needs num_batches_tracked");
+  bn_prepare_kernel<<<1, 1024, 0, stream>>>(stats, gamma, beta, coef, saved, running_mean,
+                                            running_var, C, 1.f / static_cast<float>(P), unbias,
+                                            eps, momentum, num_batches_tracked);
+  TGB_CHECK_LAUNCH("bn_prepare_tracked");
   return 0;
 }
 

@@ -28,6 +28,8 @@ void tgb_reset_launch_count(void);
  * sum of squares of y into; the caller zeroes them first.
  *   stats_mode 1: [N][K][2] per (image, channel)  - InstanceNorm statistics
  *   stats_mode 2: [K][2]    per channel           - BatchNorm statistics
+ *   stats_mode -1 / -2: as 1 / 2, and the call zeroes the accumulators itself first (all
+ *   forward entry points below accept the negative forms too)
  * Also computes the data gradient of such a convolution when called with dy as x, the
  * tap-flipped / channel-transposed weights and pad' = R-1-pad.
  * Reference call sites: nn.Conv2d forward/backward-data in benchmarks/models/{unet,resnet,
@@ -96,6 +98,12 @@ int tgb_conv2d_wgrad_tf32_noalloc(const float* dy, const float* x, float* dw,
 int tgb_moments(const float* x, float* out, int G, int P, int C, cudaStream_t stream);
 int tgb_in_prepare(const float* stats, const float* drop_scale, float* mean_coef,
                    int G, int P, int C, float eps, cudaStream_t stream);
+/* Same, with the Dropout2d mask made in the kernel: `uniform` [G][C] holds random numbers in
+ * [0,1) (from the caller's generator, so checkpoint recomputation can reproduce them); channel
+ * (g,c) is kept when uniform >= drop_p and scaled by 1/(1-drop_p). */
+int tgb_in_prepare_dropout(const float* stats, const float* uniform, float drop_p,
+                           float* mean_coef, int G, int P, int C, float eps,
+                           cudaStream_t stream);
 int tgb_in_leaky_fwd(const float* y, const float* mean_coef, float* z, int G, int P, int C,
                      float slope, cudaStream_t stream);
 int tgb_in_leaky_bwd_sums(const float* dz, const float* z, float* out, int G, int P, int C,
@@ -117,6 +125,13 @@ int tgb_in_leaky_bwd(const float* dz, const float* z, const float* mean_coef, co
 int tgb_bn_prepare(const float* stats, const float* gamma, const float* beta, float* coef,
                    float* saved, float* running_mean, float* running_var, int P, int C,
                    float eps, float momentum, cudaStream_t stream);
+/* tgb_bn_prepare that also keeps nn.BatchNorm2d's num_batches_tracked (int64, on the device):
+ * the counter is incremented by the kernel, and momentum < 0 selects the cumulative average
+ * 1 / (count after the increment) - no separate counter kernel, no host read of the counter. */
+int tgb_bn_prepare_tracked(const float* stats, const float* gamma, const float* beta,
+                           float* coef, float* saved, float* running_mean, float* running_var,
+                           long long* num_batches_tracked, int P, int C, float eps,
+                           float momentum, cudaStream_t stream);
 int tgb_bn_act_fwd(const float* y, const float* coef, float* z, int P, int C, int relu,
                    cudaStream_t stream);
 int tgb_bn_act_bwd(const float* dz, const float* y, const float* coef, const float* saved,

@@ -82,6 +82,15 @@ BIG_CONV_CASES = [
     (5, 1024, 12, 12, 1024, {'TGB_FPROP_SPLITS': '3'}),    # split-K + TMA reduce-add
     (16, 256, 24, 24, 512, {}),                           # micro-batch 16 shape of the 8-GPU run
     (2, 2048, 6, 6, 2048, {}),                            # whole small images per tile
+    # CTA pairs (tcgen05.mma.cta_group::2, M = 256): even / odd tile counts, several channel
+    # tiles, split-K, statistics with partial tiles
+    (5, 1024, 12, 12, 1024, {'TGB_FPROP_2CTA': '1'}),
+    (16, 256, 24, 24, 512, {'TGB_FPROP_2CTA': '1'}),
+    (3, 256, 20, 20, 256, {'TGB_FPROP_2CTA': '1'}),        # 3 x 4 = 12 tiles... odd rows
+    (7, 512, 12, 12, 256, {'TGB_FPROP_2CTA': '1'}),        # odd number of pixel tiles
+    (2, 2048, 6, 6, 2048, {'TGB_FPROP_2CTA': '1'}),
+    (5, 1024, 12, 12, 1024, {'TGB_FPROP_2CTA': '1', 'TGB_FPROP_SPLITS': '3'}),
+    (40, 256, 48, 48, 256, {'TGB_FPROP_2CTA': '1'}),       # many tiles per CTA pair
 ]
 
 
@@ -816,3 +825,21 @@ def test_converted_bottleneck_tail_is_one_fused_join():
     # a plain run WITHOUT checkpointing (plain BatchNorm under checkpointing updates twice).
     for (n, p), (_, q) in zip(gf.named_buffers(), once.named_buffers()):
         assert torch.allclose(p.float(), q.float(), rtol=1e-3, atol=1e-3), n
+
+
+@pytest.mark.parametrize('momentum', [0.1, None])
+def test_fused_batchnorm_keeps_counter_and_cumulative_average_on_the_device(momentum):
+    """num_batches_tracked is incremented inside the prepare kernel, and momentum=None (the
+    cumulative moving average) is resolved from that device counter - no host read."""
+    from torchgpipe_b200 import ops
+    torch.manual_seed(31)
+    plain = nn.Sequential(nn.Conv2d(8, 16, 3, padding=1, bias=False),
+                          nn.BatchNorm2d(16, momentum=momentum), nn.ReLU()).cuda()
+    fused = ops.convert_to_sm100(copy.deepcopy(plain))
+    for step in range(3):
+        x = torch.randn(4, 8, 10, 10, device='cuda') * (step + 1)
+        a, b = fused(x), plain(x)
+        assert rel_err(a, b) < 5e-3
+    assert int(fused[1].num_batches_tracked) == 3 == int(plain[1].num_batches_tracked)
+    assert torch.allclose(fused[1].running_mean, plain[1].running_mean, atol=2e-3)
+    assert torch.allclose(fused[1].running_var, plain[1].running_var, rtol=1e-2, atol=2e-3)

@@ -266,7 +266,9 @@ class DistributedGPipe:
                 'state that a graph replay does not execute')
         for m in partition.modules():
             tracks = getattr(m, 'track_running_stats', False)
-            if isinstance(m, _BatchNorm) and tracks and getattr(m, 'momentum', 0.1) is None:
+            native = type(m).__name__ == 'AbsorbedBatchNorm2d'    # counter kept on the device
+            if isinstance(m, _BatchNorm) and tracks and not native \
+                    and getattr(m, 'momentum', 0.1) is None:
                 raise ValueError(
                     'cuda_graphs=True needs BatchNorm layers with a numeric momentum: '
                     'momentum=None (cumulative average) reads num_batches_tracked on the host')
@@ -302,7 +304,7 @@ class DistributedGPipe:
         it sat waiting for activations / gradients from the neighbours (pipeline bubble plus
         any communication that was not overlapped); ``span_ms``: first pass start to last pass
         end; ``bubble_frac`` = 1 - busy/span; ``comm_ms_bound``: bytes received over the
-        measured 770 GB/s peer bandwidth - an upper bound on the exposed communication, which
+        measured peer bandwidth (``utils.link_bandwidth_gbs``: 775 GB/s) - an upper bound on the exposed communication, which
         is also bounded by ``recv_wait_ms``.
         """
         if not self._marks:
@@ -311,7 +313,8 @@ class DistributedGPipe:
         busy = sum(t1.elapsed_time(t2) for _, _, t1, t2 in self._marks)
         wait = sum(t0.elapsed_time(t1) for _, t0, t1, _ in self._marks)
         span = self._marks[0][1].elapsed_time(self._marks[-1][3])
-        comm_bound = self._bytes_received / 770e9 * 1e3
+        from torchgpipe_b200.utils import link_bandwidth_gbs
+        comm_bound = self._bytes_received / (link_bandwidth_gbs() * 1e9) * 1e3
         report = {'busy_ms': busy, 'recv_wait_ms': wait, 'span_ms': span,
                   'bubble_frac': max(0.0, 1.0 - busy / span) if span > 0 else 0.0,
                   'bytes_received': float(self._bytes_received), 'comm_ms_bound': comm_bound,

@@ -85,11 +85,12 @@ def conv2d_forward(x: Tensor, w: Tensor, padding: Tuple[int, int], stats_mode: i
         assert y.shape == (N, K, Ho, Wo) and _is_channel_slice(y), \
             'out must be a channel slice of an NHWC tensor'
         y_pixel = _pixel_stride(y)
-    stats = None
+    stats = None            # zeroed by the launch itself (negative stats_mode)
     if stats_mode == 1:
-        stats = torch.zeros((N, K, 2), device=x.device, dtype=torch.float32)
+        stats = torch.empty((N, K, 2), device=x.device, dtype=torch.float32)
     elif stats_mode == 2:
-        stats = torch.zeros((K, 2), device=x.device, dtype=torch.float32)
+        stats = torch.empty((K, 2), device=x.device, dtype=torch.float32)
+    stats_mode = -stats_mode
     with torch.cuda.device(x.device):
         if (sh, sw) == (1, 1) and y_pixel == K and out_hw is None:
             rc = lib.tgb_conv2d_fprop_tf32(_lib.ptr(x), _lib.ptr(w), _lib.ptr(y), _lib.ptr(stats),
@@ -416,11 +417,12 @@ class _StemConv2d(torch.autograd.Function):
                 cache['stem_version'], cache['stem_ptr'], cache['stem_w'] = \
                     w._version, w.data_ptr(), wv
         y = torch.empty((N, K, Ho, Wo), device=x.device, dtype=torch.float32, memory_format=_CL)
-        stats = None
+        stats = None        # zeroed by the launch itself (negative stats_mode)
         if stats_mode == 1:
-            stats = torch.zeros((N, K, 2), device=x.device, dtype=torch.float32)
+            stats = torch.empty((N, K, 2), device=x.device, dtype=torch.float32)
         elif stats_mode == 2:
-            stats = torch.zeros((K, 2), device=x.device, dtype=torch.float32)
+            stats = torch.empty((K, 2), device=x.device, dtype=torch.float32)
+        stats_mode = -stats_mode
         with torch.cuda.device(x.device):
             st = _lib.stream_ptr(x.device)
             rc = lib.tgb_stem_pack(_lib.ptr(x), _lib.ptr(xp), _c_int(N), _c_int(C), _c_int(H),
@@ -553,7 +555,7 @@ class _InstNormLeaky(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, y: Tensor, stats: Optional[Tensor], drop_scale: Optional[Tensor],  # type: ignore[override]
-                eps: float, slope: float):
+                eps: float, slope: float, drop_p: float = 0.0):
         lib = _lib.require()
         y = _cl(y)
         N, C, H, W = y.shape
@@ -566,8 +568,14 @@ class _InstNormLeaky(torch.autograd.Function):
             drop_scale = drop_scale.reshape(N, C).contiguous()
         with torch.cuda.device(y.device):
             st = _lib.stream_ptr(y.device)
-            rc = lib.tgb_in_prepare(_lib.ptr(stats), _lib.ptr(drop_scale), _lib.ptr(mean_coef),
-                                    _c_int(N), _c_int(P), _c_int(C), _c_float(eps), st)
+            if drop_p > 0.0:        # drop_scale holds uniform noise: the mask is made in-kernel
+                rc = lib.tgb_in_prepare_dropout(_lib.ptr(stats), _lib.ptr(drop_scale),
+                                                _c_float(drop_p), _lib.ptr(mean_coef), _c_int(N),
+                                                _c_int(P), _c_int(C), _c_float(eps), st)
+            else:
+                rc = lib.tgb_in_prepare(_lib.ptr(stats), _lib.ptr(drop_scale),
+                                        _lib.ptr(mean_coef), _c_int(N), _c_int(P), _c_int(C),
+                                        _c_float(eps), st)
             _lib.check(rc, 'tgb_in_prepare')
             rc = lib.tgb_in_leaky_fwd(_lib.ptr(y), _lib.ptr(mean_coef), _lib.ptr(z), _c_int(N),
                                       _c_int(P), _c_int(C), _c_float(slope), st)
@@ -594,18 +602,42 @@ class _InstNormLeaky(torch.autograd.Function):
                                       _lib.ptr(sums), _lib.ptr(dy), _c_int(N), _c_int(P),
                                       _c_int(C), _c_float(ctx.slope), st)
             _lib.check(rc, 'tgb_in_leaky_bwd')
-        return dy, None, None, None, None
+        return dy, None, None, None, None, None
 
 
 def instnorm_leaky(y: Tensor, stats: Optional[Tensor] = None, drop_scale: Optional[Tensor] = None,
-                   eps: float = 1e-5, slope: float = 0.01) -> Tensor:
+                   eps: float = 1e-5, slope: float = 0.01, drop_p: float = 0.0) -> Tensor:
     """Fused ``LeakyReLU(InstanceNorm2d(Dropout2d(y)))`` (no affine, batch statistics).
 
     ``stats`` are the per-(n,c) (sum, sum of squares) from the convolution epilogue (computed
     here if absent); ``drop_scale`` is ``[N,C]`` with entries 0 or ``1/(1-p)`` (``None`` = no
-    dropout). ``slope`` must be positive.
+    dropout). With ``drop_p > 0``, ``drop_scale`` instead holds uniform random numbers in
+    ``[0,1)`` and the keep / scale decision is made inside the prepare kernel (channel kept
+    when ``u >= drop_p``). ``slope`` must be positive.
     """
-    return _InstNormLeaky.apply(y, stats, drop_scale, float(eps), float(slope))
+    return _InstNormLeaky.apply(y, stats, drop_scale, float(eps), float(slope), float(drop_p))
+
+
+def _bn_prepare(stats: Tensor, weight: Optional[Tensor], bias: Optional[Tensor],
+                running_mean: Optional[Tensor], running_var: Optional[Tensor],
+                tracked: Optional[Tensor], P: int, C: int, eps: float, momentum: float, st):
+    """``(coef, saved)`` tables of a training-mode BatchNorm; updates the running estimates (and
+    ``tracked`` = num_batches_tracked, inside the same kernel) when they are given."""
+    lib = _lib.require()
+    coef = torch.empty((C, 2), device=stats.device, dtype=torch.float32)
+    saved = torch.empty((C, 2), device=stats.device, dtype=torch.float32)
+    if tracked is not None and running_mean is not None:
+        rc = lib.tgb_bn_prepare_tracked(_lib.ptr(stats), _lib.ptr(weight), _lib.ptr(bias),
+                                        _lib.ptr(coef), _lib.ptr(saved), _lib.ptr(running_mean),
+                                        _lib.ptr(running_var), _lib.ptr(tracked), _c_int(P),
+                                        _c_int(C), _c_float(eps), _c_float(momentum), st)
+    else:
+        rc = lib.tgb_bn_prepare(_lib.ptr(stats), _lib.ptr(weight), _lib.ptr(bias),
+                                _lib.ptr(coef), _lib.ptr(saved), _lib.ptr(running_mean),
+                                _lib.ptr(running_var), _c_int(P), _c_int(C), _c_float(eps),
+                                _c_float(momentum), st)
+    _lib.check(rc, 'tgb_bn_prepare')
+    return coef, saved
 
 
 class _BatchNormAct(torch.autograd.Function):
@@ -618,21 +650,17 @@ class _BatchNormAct(torch.autograd.Function):
     @staticmethod
     def forward(ctx, y: Tensor, stats: Tensor, weight: Optional[Tensor],  # type: ignore[override]
                 bias: Optional[Tensor], running_mean: Optional[Tensor],
-                running_var: Optional[Tensor], eps: float, momentum: float, relu: bool):
-        lib = _lib.require()
+                running_var: Optional[Tensor], eps: float, momentum: float, relu: bool,
+                tracked: Optional[Tensor] = None):
         y = _cl(y)
         N, C, H, W = y.shape
         P = N * H * W
-        coef = torch.empty((C, 2), device=y.device, dtype=torch.float32)
-        saved = torch.empty((C, 2), device=y.device, dtype=torch.float32)
         z = torch.empty_like(y, memory_format=_CL)
+        lib = _lib.require()
         with torch.cuda.device(y.device):
             st = _lib.stream_ptr(y.device)
-            rc = lib.tgb_bn_prepare(_lib.ptr(stats), _lib.ptr(weight), _lib.ptr(bias),
-                                    _lib.ptr(coef), _lib.ptr(saved), _lib.ptr(running_mean),
-                                    _lib.ptr(running_var), _c_int(P), _c_int(C), _c_float(eps),
-                                    _c_float(momentum), st)
-            _lib.check(rc, 'tgb_bn_prepare')
+            coef, saved = _bn_prepare(stats, weight, bias, running_mean, running_var, tracked, P,
+                                      C, eps, momentum, st)
             rc = lib.tgb_bn_act_fwd(_lib.ptr(y), _lib.ptr(coef), _lib.ptr(z), _c_int(P),
                                     _c_int(C), _c_int(int(relu)), st)
             _lib.check(rc, 'tgb_bn_act_fwd')
@@ -657,14 +685,18 @@ class _BatchNormAct(torch.autograd.Function):
         _lib.check(rc, 'tgb_bn_act_bwd')
         dweight = sums[:, 1].clone() if ctx.affine[0] else None
         dbias = sums[:, 0].clone() if ctx.affine[1] else None
-        return dy, None, dweight, dbias, None, None, None, None, None
+        return dy, None, dweight, dbias, None, None, None, None, None, None
 
 
 def batchnorm_act(y: Tensor, stats: Optional[Tensor], weight: Optional[Tensor],
                   bias: Optional[Tensor], running_mean: Optional[Tensor] = None,
                   running_var: Optional[Tensor] = None, eps: float = 1e-5,
-                  momentum: float = 0.1, relu: bool = False) -> Tensor:
+                  momentum: float = 0.1, relu: bool = False,
+                  tracked: Optional[Tensor] = None) -> Tensor:
     """Fused training-mode ``ReLU?(BatchNorm2d(y))``.
+
+    ``tracked``: the layer's ``num_batches_tracked`` (int64 CUDA tensor); the prepare kernel then
+    increments it, and a negative ``momentum`` selects the cumulative average 1/count.
 
     ``stats``: per-channel ``[C,2]`` (sum, sum of squares) from the convolution epilogue
     (``stats_mode=2``); computed here when ``None``. When ``running_mean``/``running_var`` are
@@ -674,7 +706,7 @@ def batchnorm_act(y: Tensor, stats: Optional[Tensor], weight: Optional[Tensor],
     if stats is None or stats.numel() == 0:
         stats = channel_moments(y)
     return _BatchNormAct.apply(y, stats, weight, bias, running_mean, running_var, float(eps),
-                               float(momentum), bool(relu))
+                               float(momentum), bool(relu), tracked)
 
 
 class _MaxPool2x2(torch.autograd.Function):
@@ -892,21 +924,17 @@ class _BatchNormAddAct(torch.autograd.Function):
     @staticmethod
     def forward(ctx, y: Tensor, stats: Tensor, weight: Optional[Tensor],  # type: ignore[override]
                 bias: Optional[Tensor], res: Tensor, running_mean: Optional[Tensor],
-                running_var: Optional[Tensor], eps: float, momentum: float, relu: bool):
+                running_var: Optional[Tensor], eps: float, momentum: float, relu: bool,
+                tracked: Optional[Tensor] = None):
         lib = _lib.require()
         y, res = _cl(y), _cl(res)
         N, C, H, W = y.shape
         P = N * H * W
-        coef = torch.empty((C, 2), device=y.device, dtype=torch.float32)
-        saved = torch.empty((C, 2), device=y.device, dtype=torch.float32)
         z = torch.empty_like(y, memory_format=_CL)
         with torch.cuda.device(y.device):
             st = _lib.stream_ptr(y.device)
-            rc = lib.tgb_bn_prepare(_lib.ptr(stats), _lib.ptr(weight), _lib.ptr(bias),
-                                    _lib.ptr(coef), _lib.ptr(saved), _lib.ptr(running_mean),
-                                    _lib.ptr(running_var), _c_int(P), _c_int(C), _c_float(eps),
-                                    _c_float(momentum), st)
-            _lib.check(rc, 'tgb_bn_prepare')
+            coef, saved = _bn_prepare(stats, weight, bias, running_mean, running_var, tracked, P,
+                                      C, eps, momentum, st)
             rc = lib.tgb_bn_add_act_fwd(_lib.ptr(y), _lib.ptr(coef), _lib.ptr(res), _lib.ptr(z),
                                         _c_int(P), _c_int(C), _c_int(int(relu)), st)
             _lib.check(rc, 'tgb_bn_add_act_fwd')
@@ -933,21 +961,22 @@ class _BatchNormAddAct(torch.autograd.Function):
         _lib.check(rc, 'tgb_bn_add_act_bwd')
         dweight = sums[:, 1].clone() if ctx.affine[0] else None
         dbias = sums[:, 0].clone() if ctx.affine[1] else None
-        return dy, None, dweight, dbias, dres, None, None, None, None, None
+        return dy, None, dweight, dbias, dres, None, None, None, None, None, None
 
 
 def batchnorm_add_act(y: Tensor, stats: Optional[Tensor], weight: Optional[Tensor],
                       bias: Optional[Tensor], res: Tensor,
                       running_mean: Optional[Tensor] = None,
                       running_var: Optional[Tensor] = None, eps: float = 1e-5,
-                      momentum: float = 0.1, relu: bool = True) -> Tensor:
+                      momentum: float = 0.1, relu: bool = True,
+                      tracked: Optional[Tensor] = None) -> Tensor:
     """Fused training-mode ``ReLU?(BatchNorm2d(y) + res)`` (``bn3 -> residual -> relu3`` of a
     bottleneck, reference ``benchmarks/models/resnet/bottleneck.py:31-79``). Arguments as
     :func:`batchnorm_act`."""
     if stats is None or stats.numel() == 0:
         stats = channel_moments(y)
     return _BatchNormAddAct.apply(y, stats, weight, bias, res, running_mean, running_var,
-                                  float(eps), float(momentum), bool(relu))
+                                  float(eps), float(momentum), bool(relu), tracked)
 
 
 _PLAN_FIELDS = ('BN', 'BW', 'BH', 'BNB', 'tiles_w', 'tiles_h', 'tiles_n', 'tiles_k', 'splits',

@@ -121,11 +121,13 @@ class ConvInstNormLeaky(nn.Module):
         TF.refresh_dgrad_weight(self.weight, self._cache)
         TF.refresh_stem_weight(self.weight, self._cache)
 
-    def _drop_scale(self, n: int, device: torch.device) -> Optional[Tensor]:
+    def _drop_noise(self, n: int, device: torch.device) -> Optional[Tensor]:
+        """Uniform noise for the channel dropout (one launch, PyTorch's CUDA generator, so
+        checkpoint recomputation and graph replays reproduce it); the keep / scale decision is
+        made inside the normalisation's prepare kernel."""
         if not self.training or self.p == 0.0:
             return None
-        keep = torch.rand(n, self.out_channels, device=device) >= self.p
-        return keep.to(torch.float32).mul_(1.0 / (1.0 - self.p))
+        return torch.rand(n, self.out_channels, device=device)
 
     def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
         if not (input.is_cuda and input.dtype == torch.float32):
@@ -133,13 +135,14 @@ class ConvInstNormLeaky(nn.Module):
             y = F.dropout2d(y, self.p, self.training)
             return F.leaky_relu(F.instance_norm(y, eps=self.eps), self.slope)
 
-        scale = self._drop_scale(input.size(0), input.device)
+        noise = self._drop_noise(input.size(0), input.device)
         got = _conv_any(input, self.weight, self.stride, self.padding, 1, self._cache)
         if got is None:         # no native path (odd output channels): library convolution
             x = input.contiguous(memory_format=_CL)
             got = F.conv2d(x, self.weight, None, self.stride, self.padding), None
         y, stats = got
-        return TF.instnorm_leaky(y, stats, scale, self.eps, self.slope)
+        return TF.instnorm_leaky(y, stats, noise, self.eps, self.slope,
+                                 drop_p=self.p if noise is not None else 0.0)
 
 
 class AbsorbedBatchNorm2d(nn.BatchNorm2d):
@@ -194,17 +197,18 @@ class AbsorbedBatchNorm2d(nn.BatchNorm2d):
 
 def _bn_running_args(bn: AbsorbedBatchNorm2d, stats: Tensor, count: int):
     """What the fused kernels need to keep ``bn``'s running estimates: ``(running_mean,
-    running_var, momentum)`` - ``(None, None, 0)`` while recomputing, without tracking, or under
-    DeferredBatchNorm (whose accumulation happens here as a side effect)."""
+    running_var, momentum, num_batches_tracked)`` - ``(None, None, 0, None)`` while recomputing,
+    without tracking, or under DeferredBatchNorm (whose accumulation happens here as a side
+    effect)."""
     if bn.track_running_stats and not is_recomputing():
         if bn.deferred_chunks:
             bn.track(stats, count)
         else:
-            bn.num_batches_tracked += 1
-            momentum = (1.0 / float(bn.num_batches_tracked) if bn.momentum is None
-                        else bn.momentum)
-            return bn.running_mean, bn.running_var, momentum
-    return None, None, 0.0
+            # the prepare kernel increments num_batches_tracked itself; momentum None (the
+            # cumulative average) is passed as -1 and resolved on the device from that counter
+            momentum = -1.0 if bn.momentum is None else float(bn.momentum)
+            return bn.running_mean, bn.running_var, momentum, bn.num_batches_tracked
+    return None, None, 0.0, None
 
 
 def _bn_torch(bn: AbsorbedBatchNorm2d, y: Tensor) -> Tensor:
@@ -280,10 +284,10 @@ class ConvBatchNormAct(nn.Module):
         if self.defer:
             return y, stats
 
-        running_mean, running_var, momentum = _bn_running_args(bn, stats,
-                                                               y.numel() // y.size(1))
+        running_mean, running_var, momentum, tracked = _bn_running_args(bn, stats,
+                                                                        y.numel() // y.size(1))
         return TF.batchnorm_act(y, stats, bn.weight, bn.bias, running_mean, running_var, bn.eps,
-                                momentum, self.relu)
+                                momentum, self.relu, tracked)
 
 
 def _bn_apply(bn: AbsorbedBatchNorm2d, y: Tensor, stats: Optional[Tensor], relu: bool) -> Tensor:
@@ -291,9 +295,10 @@ def _bn_apply(bn: AbsorbedBatchNorm2d, y: Tensor, stats: Optional[Tensor], relu:
     estimates (or DeferredBatchNorm accumulators) kept up to date."""
     if stats is None:
         stats = TF.channel_moments(y)
-    running_mean, running_var, momentum = _bn_running_args(bn, stats, y.numel() // y.size(1))
+    running_mean, running_var, momentum, tracked = _bn_running_args(bn, stats,
+                                                                    y.numel() // y.size(1))
     return TF.batchnorm_act(y, stats, bn.weight, bn.bias, running_mean, running_var, bn.eps,
-                            momentum, relu)
+                            momentum, relu, tracked)
 
 
 class AmoebaStem(nn.Module):
@@ -480,10 +485,10 @@ def _make_residual():
             if stats.numel() == 0 or not bn.training:       # ATen path (CPU / eval)
                 z = _bn_torch(bn, y) + identity
                 return F.relu(z) if self.relu else z
-            running_mean, running_var, momentum = _bn_running_args(bn, stats,
-                                                                   y.numel() // y.size(1))
+            running_mean, running_var, momentum, tracked = _bn_running_args(
+                bn, stats, y.numel() // y.size(1))
             return TF.batchnorm_add_act(y, stats, bn.weight, bn.bias, identity, running_mean,
-                                        running_var, bn.eps, momentum, self.relu)
+                                        running_var, bn.eps, momentum, self.relu, tracked)
 
     return BatchNormResidualAct
 
