@@ -6,6 +6,10 @@ portals for skip tensors.
     python benchmarks/timeline.py dep-str-x     # skips travel through every stage as tuples
     python benchmarks/timeline.py dep-x-x       # ... and copies run on the compute streams
     python benchmarks/timeline.py baseline      # ... and no backward ordering edges
+    python benchmarks/timeline.py product       # all mechanisms + sm_100a operators + CUDA graphs
+
+The four ablation rows run the same PyTorch operators (the ablation is about the pipeline's
+mechanisms, as in the reference); ``product`` is the path a user of this repository gets.
 
 4 stages, batch 128, 8 micro-batches, balance [34,76,70,61] (reference main.py:146-166). Reports
 samples/s, mean GPU utilisation sampled with nvidia-smi (reference gpu_utils.py) and peak memory.
@@ -23,7 +27,10 @@ from torch.optim import SGD
 from common import device_timed, emit, load_impl
 
 EXPERIMENTS = {'baseline': (False, False, False), 'dep-x-x': (True, False, False),
-               'dep-str-x': (True, True, False), 'dep-str-ptl': (True, True, True)}
+               'dep-str-x': (True, True, False), 'dep-str-ptl': (True, True, True),
+               # everything on, plus what this repository adds: the sm_100a operators and
+               # CUDA-graph replay of every stage pass (GPipe(cuda_graphs=True))
+               'product': (True, True, True)}
 
 
 class UtilSampler:
@@ -112,15 +119,17 @@ def main():
     torch.manual_seed(0)
     model = builders['unet'](depth=5, num_convs=5, base_channels=16 if args.smoke else 64)
     balance = [34, 76, 70, 61]
+    product = args.experiment == 'product'
     if not use_portals:
         model = tuplify_skips(model)
-    elif not args.smoke:
+    elif product and not args.smoke:
         model = convert(model)
     batch, chunks, hw = (8, 4, 64) if args.smoke else (128, 8, 192)
     devices = ([torch.device(d if d.startswith('c') else f'cuda:{d}')
                 for d in args.devices.split(',')] if args.devices
                else [torch.device('cuda', i) for i in range(4)])
-    pipe = GPipe(model, balance, devices=devices, chunks=chunks)
+    pipe = GPipe(model, balance, devices=devices, chunks=chunks,
+                 **({'cuda_graphs': True} if product and devices[0].type == 'cuda' else {}))
     if not use_dep:
         rp.depend = lambda fork_from, join_to: None         # no backward ordering edges
     if not use_streams:

@@ -216,15 +216,28 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
         }
         int tap = it_begin / g.c_blocks;
         int cb = it_begin - tap * g.c_blocks;
-        for (int it = it_begin; it < it_end; ++it) {
-          const int r = tap / g.S;
-          const int s = tap - r * g.S;
-          // tap offset = stride * q + p: box origin moves by q inside the parity-p view of X
+        // Per-tap quantities are recomputed only when the tap changes (the producer thread has
+        // one MMA-iteration of time per stage; integer divisions here would bound narrow tiles).
+        // tap offset = stride * q + p: box origin moves by q inside the parity-p view of X.
+        const bool unit_stride = g.stride_h == 1 && g.stride_w == 1;
+        int qr = 0, qs = 0;
+        const CUtensorMap* mx = &tmap_x;
+        auto enter_tap = [&](int t) {
+          const int r = t / g.S;
+          const int s = t - r * g.S;
           const int ar = r - g.pad_h, as = s - g.pad_w;
-          const int qr = floor_div(ar, g.stride_h), qs = floor_div(as, g.stride_w);
-          const int view = (ar - qr * g.stride_h) * g.stride_w + (as - qs * g.stride_w);
-          const CUtensorMap* mx = view == 0 ? &tmap_x : view == 1 ? &tmap_x1
-                                : view == 2 ? &tmap_x2 : &tmap_x3;
+          if (unit_stride) {
+            qr = ar;
+            qs = as;
+          } else {
+            qr = floor_div(ar, g.stride_h);
+            qs = floor_div(as, g.stride_w);
+            const int view = (ar - qr * g.stride_h) * g.stride_w + (as - qs * g.stride_w);
+            mx = view == 0 ? &tmap_x : view == 1 ? &tmap_x1 : view == 2 ? &tmap_x2 : &tmap_x3;
+          }
+        };
+        enter_tap(tap);
+        for (int it = it_begin; it < it_end; ++it) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* a_dst = smem + stage * L::kStageBytes;
           uint8_t* b_dst = a_dst + L::kABytes;
@@ -238,7 +251,7 @@ conv_fprop_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x,
           }
           if (++cb == g.c_blocks) {
             cb = 0;
-            ++tap;
+            enter_tap(++tap);
           }
         }
       }
@@ -570,14 +583,25 @@ conv_fprop_tf32_pair_kernel(const __grid_constant__ CUtensorMap tmap_x,
         const int k0 = kt * BN + static_cast<int>(rank) * (BN / 2);   // this CTA's half of B
         int tap = it_begin / g.c_blocks;
         int cb = it_begin - tap * g.c_blocks;
-        for (int it = it_begin; it < it_end; ++it) {
-          const int r = tap / g.S;
-          const int s = tap - r * g.S;
+        const bool unit_stride = g.stride_h == 1 && g.stride_w == 1;
+        int qr = 0, qs = 0;
+        const CUtensorMap* mx = &tmap_x;
+        auto enter_tap = [&](int t) {       // per-tap work only when the tap changes
+          const int r = t / g.S;
+          const int s = t - r * g.S;
           const int ar = r - g.pad_h, as = s - g.pad_w;
-          const int qr = floor_div(ar, g.stride_h), qs = floor_div(as, g.stride_w);
-          const int view = (ar - qr * g.stride_h) * g.stride_w + (as - qs * g.stride_w);
-          const CUtensorMap* mx = view == 0 ? &tmap_x : view == 1 ? &tmap_x1
-                                : view == 2 ? &tmap_x2 : &tmap_x3;
+          if (unit_stride) {
+            qr = ar;
+            qs = as;
+          } else {
+            qr = floor_div(ar, g.stride_h);
+            qs = floor_div(as, g.stride_w);
+            const int view = (ar - qr * g.stride_h) * g.stride_w + (as - qs * g.stride_w);
+            mx = view == 0 ? &tmap_x : view == 1 ? &tmap_x1 : view == 2 ? &tmap_x2 : &tmap_x3;
+          }
+        };
+        enter_tap(tap);
+        for (int it = it_begin; it < it_end; ++it) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* a_dst = smem + stage * L::kStageBytes;
           uint8_t* b_dst = a_dst + L::kABytes;
@@ -591,7 +615,7 @@ conv_fprop_tf32_pair_kernel(const __grid_constant__ CUtensorMap tmap_x,
           }
           if (++cb == g.c_blocks) {
             cb = 0;
-            ++tap;
+            enter_tap(++tap);
           }
         }
       }
@@ -1027,8 +1051,20 @@ static int run_fprop(const ConvProblem& p_in, cudaStream_t stream) {
                           halo, resident))
     return rc;
   const int sms = sm_count();
-  const bool stats_after = g.splits > 1 && g.stats_mode != 0;
+  // Per-channel statistics (mode 2) from the epilogue are 2*K addresses - a handful of cache
+  // lines - that EVERY pixel tile adds into; the L2 serialises atomics on one line (measured
+  // about 0.7 us per pixel tile). With a long reduction per tile that stays hidden behind the
+  // MMAs; with a short one it is exposed (ResNet 1x1/2 projection 512->1024 at micro-batch 110:
+  // 0.048 ms without statistics, 0.169 ms with). Then one streaming pass over the freshly
+  // written Y (mostly L2 hits) is cheaper. Per-image statistics (mode 1) spread over N times as
+  // many lines and keep the fused path.
+  const bool contended = g.stats_mode == 2 && !halo && y_dense &&
+                         static_cast<long>(p.R) * p.S * g.c_blocks * g.tiles_k < 400 &&
+                         g.tiles_w * g.tiles_h * g.tiles_n > 16 &&
+                         getenv("TGB_FPROP_FUSED_STATS") == nullptr;
+  const bool stats_after = (g.splits > 1 || contended) && g.stats_mode != 0;
   const int stats_mode_req = g.stats_mode;
+  if (contended) g.stats_mode = 0;
   if (g.splits > 1) {
     g.stats_mode = 0;         // partial tiles cannot produce sum of squares: tgb_moments below
     cudaError_t e = cudaMemsetAsync(p.y, 0, static_cast<size_t>(p.N) * g.Ho * g.Wo * p.K * 4,

@@ -59,8 +59,8 @@ def main():
     torch.backends.cudnn.allow_tf32 = True
     torch.backends.cudnn.benchmark = True
     flush = torch.empty(64 << 20, device='cuda')
-    print(f'{"layer":<18}{"GFLOP":>8} | {"fwd ours":>9}{"cudnn":>8} | {"dgrad ours":>11}{"cudnn":>8} | '
-          f'{"wgrad ours":>11}{"cudnn":>8}   (ms)')
+    print(f'{"layer":<18}{"GFLOP":>8} | {"fwd+stats":>9}{"fwd":>8}{"cudnn":>8} | {"dgrad ours":>11}'
+          f'{"cudnn":>8} | {"wgrad ours":>11}{"cudnn":>8}   (ms)')
     for name, N, C, H, W, K, (R, S), stride, pad in SHAPES[which]:
         x = torch.randn(N, C, H, W, device='cuda').contiguous(memory_format=CL)
         w = (torch.randn(K, C, R, S, device='cuda') / (C * R * S) ** 0.5).contiguous(
@@ -70,6 +70,7 @@ def main():
         cache = {}
         gflop = 2.0 * y.numel() * C * R * S / 1e9
         f_o = timed(lambda: TF.conv2d_forward(x, w, pad, 2, stride), flush)
+        f_n = timed(lambda: TF.conv2d_forward(x, w, pad, 0, stride), flush)
         f_c = timed(lambda: F.conv2d(x, w, stride=stride, padding=pad), flush)
         d_o = timed(lambda: TF.conv2d_dgrad(dy, w, x.shape, pad, stride, cache), flush)
         d_c = timed(lambda: torch.nn.grad.conv2d_input(x.shape, w, dy, stride=stride,
@@ -77,7 +78,7 @@ def main():
         w_o = timed(lambda: TF._conv2d_wgrad(dy, x, w.shape, pad, stride), flush)
         w_c = timed(lambda: torch.nn.grad.conv2d_weight(x, w.shape, dy, stride=stride,
                                                         padding=pad), flush)
-        print(f'{name:<18}{gflop:8.1f} | {f_o:9.3f}{f_c:8.3f} | {d_o:11.3f}{d_c:8.3f} | '
+        print(f'{name:<18}{gflop:8.1f} | {f_o:9.3f}{f_n:8.3f}{f_c:8.3f} | {d_o:11.3f}{d_c:8.3f} | '
               f'{w_o:11.3f}{w_c:8.3f}')
 
 

@@ -2,10 +2,11 @@
 
     python tools/roofline.py profiles/unet_layers_selftest.txt > profiles/roofline_unet_layers.md
 
-Denominators are the MEASURED peaks of the box (``MEASURED_PEAKS.json``): HBM copy bandwidth and
-the cuBLAS bf16 burst throughput; the TF32 roof is taken as half of the bf16 one (same tensor
-cores, twice the bytes per element). A 3x3 stride-1 convolution layer does 2*N*H*W*C*K*9 FLOP and
-must move at least its input, its output and its weights once (fp32).
+Denominators are MEASURED on the box: HBM copy bandwidth from ``MEASURED_PEAKS.json`` (driver-
+written) and the TF32 roof from ``profiles/measured_tf32_peak.json`` (``tools/
+measure_tf32_peak.py``: cuBLAS fp32 matmul with TF32 allowed, burst figure); when that file is
+missing, half of the cuBLAS bf16 burst throughput. A 3x3 stride-1 convolution layer does
+2*N*H*W*C*K*9 FLOP and must move at least its input, its output and its weights once (fp32).
 """
 import json
 import os
@@ -24,6 +25,14 @@ def main() -> None:
     except OSError:
         peaks = {'hbm_gbs': 6557.8, 'bf16_tflops': 1651.1}
     tf32_peak = peaks['bf16_tflops'] / 2.0          # TFLOP/s
+    tf32_note = f'half of the cuBLAS bf16 burst {peaks["bf16_tflops"]:.0f}'
+    try:
+        measured = json.load(open(os.path.join(ROOT, 'profiles', 'measured_tf32_peak.json')))
+        tf32_peak = measured['tf32_tflops_burst']
+        tf32_note = (f'measured: cuBLAS TF32 matmul 8192^3, burst; sustained '
+                     f'{measured["tf32_tflops_sustained"]:.0f}')
+    except (OSError, KeyError, ValueError):
+        pass
     hbm = peaks['hbm_gbs']                          # GB/s
     rows = {}
     for line in open(table):
@@ -33,8 +42,8 @@ def main() -> None:
         kind = 'wgrad' if m.group(1) else ('fprop+stats' if m.group(6) == '1' else 'fprop')
         key = tuple(int(m.group(i)) for i in (2, 3, 4))
         rows.setdefault(key, {})[kind] = float(m.group(7))
-    print(f'Roofline against measured peaks: TF32 {tf32_peak:.0f} TFLOP/s (half of the cuBLAS bf16 '
-          f'burst {peaks["bf16_tflops"]:.0f}), HBM {hbm:.0f} GB/s; micro-batch {batch}.\n')
+    print(f'Roofline against measured peaks: TF32 {tf32_peak:.0f} TFLOP/s ({tf32_note}), '
+          f'HBM {hbm:.0f} GB/s; micro-batch {batch}.\n')
     print('| C -> K @ HxW | GFLOP | min MB | roof ms (compute / memory) | fprop ms (% of roof) | '
           'fprop+stats | wgrad |')
     print('|---|---|---|---|---|---|---|')
