@@ -209,9 +209,16 @@ def test_small_channel_stem_vs_fp32(case):
     assert rel_err(stats[..., 0], ref.sum((2, 3))) < 5e-3 or \
         torch.allclose(stats[..., 0], ref.sum((2, 3)), atol=0.05)
     g = torch.randn_like(ref)
-    dw, = torch.autograd.grad(y, w, g)
-    rdw, = torch.autograd.grad(ref, w, g)
+    dw, = torch.autograd.grad(y, w, g, retain_graph=True)
+    rdw, = torch.autograd.grad(ref, w, g, retain_graph=True)
     assert rel_err(dw, rdw) < 2e-3
+    # gradient with respect to the image (the eager pipeline asks for it at the first stage)
+    xg = x.detach().clone().requires_grad_()
+    yg, _ = TF.stem_conv2d(xg, w, pad, stride)
+    dx, = torch.autograd.grad(yg, xg, g)
+    xr = x.detach().clone().requires_grad_()
+    rdx, = torch.autograd.grad(F.conv2d(xr, w, stride=stride, padding=pad), xr, g)
+    assert rel_err(dx, rdx) < 2e-3
     # cached packed weights follow an in-place parameter update
     with torch.no_grad():
         w.mul_(0.5)

@@ -11,8 +11,9 @@ from typing import List, Tuple
 
 from torch import nn
 
-from torchgpipe_b200.ops.modules import (Absorbed, AbsorbedBatchNorm2d, AmoebaFactorizedReduce,
-                                         AmoebaStem, BatchNormResidualAct,
+from torchgpipe_b200.ops.modules import (Absorbed, AbsorbedBatchNorm2d, AmoebaCell,
+                                         AmoebaFactorizedReduce, AmoebaStem,
+                                         BatchNormResidualAct,
                                          Conv2dTC, ConvBatchNormAct, ConvInstNormLeaky,
                                          GlobalAvgPoolNHWC, LinearTC, MaxPool2x2, Pool2dNHWC,
                                          UpsamplePopCat)
@@ -121,6 +122,15 @@ def _is_amoeba_stem(m: nn.Module) -> bool:
             and type(m.bn) is nn.BatchNorm2d and _plain_conv(m.conv))
 
 
+def _is_amoeba_cell(m: nn.Module) -> bool:
+    """AmoebaNet-D cell (reference amoebanet/__init__.py:97-136): two input reductions, a
+    ModuleList of genotype operations, pair indices and the list of states to concatenate."""
+    return (type(m).__name__ == 'Cell' and _children(m) == ['reduce1', 'reduce2', 'operations']
+            and isinstance(m.operations, nn.ModuleList) and len(m.operations) % 2 == 0
+            and hasattr(m, 'indices') and len(m.indices) == len(m.operations)
+            and hasattr(m, 'concat'))
+
+
 def _is_factorized_reduce(m: nn.Module) -> bool:
     """AmoebaNet's stride-2 reduction (reference amoebanet/operations.py:24-40)."""
     if type(m).__name__ != 'FactorizedReduce' or \
@@ -211,8 +221,14 @@ def _convert_any(module: nn.Module) -> nn.Module:
         return module
     if type(module) is nn.Sequential:
         return _convert_sequential(module)
-    if isinstance(module, (AmoebaStem, AmoebaFactorizedReduce)):
+    if isinstance(module, (AmoebaStem, AmoebaFactorizedReduce, AmoebaCell)):
         return module
+    if _is_amoeba_cell(module):
+        for name, child in list(module.named_children()):       # operations, reductions first
+            new = _convert_any(child)
+            if new is not child:
+                setattr(module, name, new)
+        return AmoebaCell(module)
     if _is_amoeba_stem(module):
         return AmoebaStem(module)
     if _is_factorized_reduce(module):

@@ -389,7 +389,8 @@ def _stem_weight(w: Tensor) -> Tensor:
 class _StemConv2d(torch.autograd.Function):
     """Convolution of an image with 1-4 channels (any layout) on the packed-window tcgen05 path
     (``csrc/conv_small.cu``). Saves the packed image (4 channels, zero halo) for the weight
-    gradient; the data gradient (rarely needed: the input is data) uses ATen."""
+    gradient; the data gradient (rarely needed: the input is data) runs the general tcgen05
+    data-gradient kernels on the filter bank padded to 4 input channels."""
 
     @staticmethod
     def forward(ctx, x: Tensor, w: Tensor, ph: int, pw: int, sh: int, sw: int,  # type: ignore[override]
@@ -398,7 +399,6 @@ class _StemConv2d(torch.autograd.Function):
         N, C, H, W = x.shape
         K, _, R, S = w.shape
         Ho, Wo = _out_hw(H, W, R, S, (ph, pw), (sh, sw))
-        assert not (relu_input and x.requires_grad), 'relu_input is for data inputs'
 
         Hp, Wp = H + 2 * ph, W + 2 * pw - S + 8
         xp = torch.empty((N, Hp, Wp, 4), device=x.device, dtype=torch.float32)
@@ -437,6 +437,7 @@ class _StemConv2d(torch.autograd.Function):
             _lib.check(rc, 'tgb_conv2d_stem_fprop_tf32')
         ctx.save_for_backward(xp, w, x if x.requires_grad else x.new_empty(0))
         ctx.geom = (N, C, H, W, K, R, S, ph, pw, sh, sw, Hp, Wp)
+        ctx.relu_input = bool(relu_input)
         if stats is None:
             stats = x.new_empty(0)
         ctx.mark_non_differentiable(stats)
@@ -467,8 +468,15 @@ class _StemConv2d(torch.autograd.Function):
             dw = dwv.view(K, R, 8, 4)[:, :, :S, :C].permute(0, 3, 1, 2).contiguous(
                 memory_format=_CL)
         if ctx.needs_input_grad[0]:
-            dx = torch.nn.grad.conv2d_input((N, C, H, W), w, dy, stride=(sh, sw),
-                                            padding=(ph, pw))
+            # Rarely wanted (the input is data), but the eager pipeline's ordering edges make
+            # the first stage's micro-batches "require grad": the general data-gradient kernels
+            # on the filter bank padded to 4 input channels, then drop the padding channels.
+            w4 = torch.zeros((K, 4, R, S), device=w.device, dtype=torch.float32).contiguous(
+                memory_format=_CL)
+            w4[:, :C] = w.detach()
+            dx = conv2d_dgrad(dy, w4, (N, 4, H, W), (ph, pw), (sh, sw), None)[:, :C]
+            if ctx.relu_input:
+                dx = dx * (x > 0)
         return dx, dw, None, None, None, None, None, None, None
 
 
@@ -477,7 +485,7 @@ def stem_conv2d(x: Tensor, w: Tensor, padding: Tuple[int, int], stride: Tuple[in
                 ) -> Tuple[Tensor, Optional[Tensor]]:
     """Convolution of a 1-4 channel image (NCHW or channels-last, fp32 CUDA) with filter rows of
     at most 8 taps, on the packed-window tcgen05 path. Returns ``(y, stats or None)``.
-    ``relu_input``: convolve ``relu(x)`` (folded into the packing pass; ``x`` must be data)."""
+    ``relu_input``: convolve ``relu(x)`` (the ReLU is folded into the packing pass)."""
     assert x.size(1) <= 4 and w.size(3) <= 8 and padding[0] >= 0 and padding[1] >= 0
     y, stats = _StemConv2d.apply(x, w, int(padding[0]), int(padding[1]), int(stride[0]),
                                  int(stride[1]), int(stats_mode), cache, bool(relu_input))

@@ -10,7 +10,7 @@ from torchgpipe_b200.ops import functional as TF
 
 __all__ = ['Absorbed', 'ConvInstNormLeaky', 'Conv2dTC', 'ConvBatchNormAct', 'AbsorbedBatchNorm2d',
            'MaxPool2x2', 'UpsamplePopCat', 'LinearTC', 'Pool2dNHWC', 'GlobalAvgPoolNHWC',
-           'BatchNormResidualAct', 'AmoebaStem', 'AmoebaFactorizedReduce']
+           'BatchNormResidualAct', 'AmoebaStem', 'AmoebaFactorizedReduce', 'AmoebaCell']
 
 _CL = torch.channels_last
 
@@ -262,7 +262,9 @@ class ConvBatchNormAct(nn.Module):
         # a deferring layer only hands (convolution, statistics) on: it may sit in another stage
         return [] if self.defer else [self.bn]
 
-    def forward(self, input: Tensor):  # type: ignore[override]
+    def forward(self, input: Tensor, add: Optional[Tensor] = None):  # type: ignore[override]
+        """``add`` (optional, not with ``defer``): a tensor of the output's shape that is added
+        after the normalisation and before the ReLU, inside the normalisation kernel."""
         bn = self.bn
         native = (input.is_cuda and input.dtype == torch.float32
                   and self.out_channels % 4 == 0)
@@ -272,6 +274,8 @@ class ConvBatchNormAct(nn.Module):
             if self.defer:
                 return y, y.new_empty(0)
             y = _bn_torch(bn, y)
+            if add is not None:
+                y = y + add
             return F.relu(y) if self.relu else y
 
         got = _conv_any(input, self.weight, self.stride, self.padding, 2, self._cache)
@@ -286,6 +290,10 @@ class ConvBatchNormAct(nn.Module):
 
         running_mean, running_var, momentum, tracked = _bn_running_args(bn, stats,
                                                                         y.numel() // y.size(1))
+        if add is not None:
+            # relu?(BatchNorm(conv) + add) in the one normalisation pass (a sum of two branches)
+            return TF.batchnorm_add_act(y, stats, bn.weight, bn.bias, add, running_mean,
+                                        running_var, bn.eps, momentum, self.relu, tracked)
         return TF.batchnorm_act(y, stats, bn.weight, bn.bias, running_mean, running_var, bn.eps,
                                 momentum, self.relu, tracked)
 
@@ -319,7 +327,6 @@ class AmoebaStem(nn.Module):
     def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
         conv, bn = self.conv, self.bn
         native = (input.is_cuda and input.dtype == torch.float32 and bn.training
-                  and not input.requires_grad
                   and TF.conv_kind(conv.in_channels, conv.out_channels, conv.kernel_size,
                                    conv.stride, conv.dilation, conv.groups) == 'stem')
         if not native:
@@ -364,6 +371,109 @@ class AmoebaFactorizedReduce(nn.Module):
         y, stats = TF.factorized_reduce_conv(x, self.conv1.weight, self.conv2.weight,
                                              self._cache1, self._cache2)
         return _bn_apply(bn, y, stats, relu=False)
+
+
+class AmoebaCell(nn.Module):
+    """An AmoebaNet-D ``Cell`` (reference ``benchmarks/models/amoebanet/__init__.py:97-136``) with
+    the work between its operations fused:
+
+    * every genotype operation starts with a ReLU of one of the cell's states, and several
+      operations read the same state - the ReLU of a state is computed once and shared
+      (the reference applies it once per operation: ``__init__.py:27``, 275 ReLUs in (18,256));
+    * ``ops[k](a) + ops[k+1](b)`` (``__init__.py:132``): when one of the two branches ends in
+      convolution + BatchNorm, the sum is folded into that BatchNorm's normalisation kernel
+      (``relu?(bn(y) + other)`` in one pass) instead of a separate elementwise add.
+
+    Children, their names and parameters are those of the original cell (``reduce1``,
+    ``reduce2``, ``operations``), so ``state_dict`` keys and layer counts do not change. The
+    final ``torch.cat`` of the chosen states stays (one copy per cell).
+    """
+
+    def __init__(self, cell: nn.Module) -> None:
+        super().__init__()
+        self.reduce1, self.reduce2, self.operations = cell.reduce1, cell.reduce2, cell.operations
+        self.indices, self.concat = tuple(cell.indices), list(cell.concat)
+
+    def extra_repr(self) -> str:
+        return f'indices: {self.indices}, fused'
+
+    # an operation's body as (needs_relu_input, callable(relu'd or raw input, add) -> output)
+    @staticmethod
+    def _leading_relu(body: nn.Module) -> bool:
+        return (isinstance(body, AmoebaFactorizedReduce)
+                or (type(body) is nn.Sequential and len(body) > 0 and type(body[0]) is nn.ReLU))
+
+    @staticmethod
+    def _can_join(body: nn.Module) -> bool:
+        """Ends in a (non-deferring) convolution + BatchNorm without ReLU: a sum can be folded in."""
+        if type(body) is not nn.Sequential:
+            return False
+        convs = [m for m in body if isinstance(m, ConvBatchNormAct)]
+        return bool(convs) and not convs[-1].relu and not convs[-1].defer \
+            and isinstance(body[len(body) - 1], AbsorbedBatchNorm2d) \
+            and body[len(body) - 2] is convs[-1]
+
+    @staticmethod
+    def _run(body: nn.Module, x: Tensor, relu_done: bool, add: Optional[Tensor]) -> Tensor:
+        if isinstance(body, AmoebaFactorizedReduce):
+            out = body(x, relu_done=relu_done)
+            return out if add is None else out + add
+        if type(body) is nn.Sequential:
+            layers = list(body)
+            if relu_done and layers and type(layers[0]) is nn.ReLU:
+                layers = layers[1:]
+            last_conv = None
+            if add is not None:
+                last_conv = len(layers) - 2         # [..., ConvBatchNormAct, AbsorbedBatchNorm2d]
+            for i, layer in enumerate(layers):
+                x = layer(x, add=add) if i == last_conv else layer(x)
+            return x
+        out = body(x)
+        return out if add is None else out + add
+
+    def forward(self, input_or_states):  # type: ignore[override]
+        if isinstance(input_or_states, tuple):
+            s1, s2 = input_or_states
+        else:
+            s1 = s2 = input_or_states
+        skip = s1
+        relu_of: dict = {}
+
+        def relu(t: Tensor) -> Tensor:
+            got = relu_of.get(id(t))
+            if got is None:
+                got = relu_of[id(t)] = (t, F.relu(t))       # keep t alive: ids are reused
+            return got[1]
+
+        def feed(body: nn.Module, t: Tensor):
+            return (relu(t), True) if self._leading_relu(body) else (t, False)
+
+        def unwrap(op: nn.Module) -> nn.Module:
+            return op.module if hasattr(op, 'module') and hasattr(op, 'name') else op
+
+        x1, d1 = feed(self.reduce1, s1)
+        x2, d2 = feed(self.reduce2, s2)
+        states = [self._run(self.reduce1, x1, d1, None), self._run(self.reduce2, x2, d2, None)]
+
+        ops, idx = self.operations, self.indices
+        for k in range(0, len(ops), 2):
+            a, b = unwrap(ops[k]), unwrap(ops[k + 1])
+            ia, ib = states[idx[k]], states[idx[k + 1]]
+            if self._can_join(b):               # a first, folded into b's last BatchNorm
+                xa, da = feed(a, ia)
+                out_a = self._run(a, xa, da, None)
+                xb, db = feed(b, ib)
+                states.append(self._run(b, xb, db, out_a))
+            elif self._can_join(a):
+                xb, db = feed(b, ib)
+                out_b = self._run(b, xb, db, None)
+                xa, da = feed(a, ia)
+                states.append(self._run(a, xa, da, out_b))
+            else:
+                xa, da = feed(a, ia)
+                xb, db = feed(b, ib)
+                states.append(self._run(a, xa, da, None) + self._run(b, xb, db, None))
+        return torch.cat([states[i] for i in self.concat], dim=1), skip
 
 
 class MaxPool2x2(nn.Module):
