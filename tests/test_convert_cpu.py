@@ -143,3 +143,83 @@ def test_forward_convolution_plans_are_pinned():
     assert not p['halo'] and p['Ho'] == 1 and p['tiles_k'] * p['BN'] >= 1000
     with pytest.raises(RuntimeError, match='C % 4'):
         conv2d_plan(1, 3, 8, 8, 64)
+
+
+def test_conv_kind_routes_every_benchmark_convolution_to_a_native_path():
+    from torchgpipe_b200.ops import functional as TF
+    # (c_in, c_out, kernel, stride) -> path; reference call sites in the comments
+    cases = [
+        ((3, 64, 7, 2), 'stem'),            # resnet/__init__.py:55
+        ((3, 64, 3, 2), 'stem'),            # amoebanet/__init__.py:54
+        ((3, 64, 3, 1), 'stem'),            # unet/__init__.py:44, first cell
+        ((64, 1, 1, 1), 'head'),            # unet/__init__.py:138
+        ((256, 512, 1, 2), 'tc'),           # resnet/__init__.py:41
+        ((128, 128, 3, 2), 'tc'),           # resnet/bottleneck.py:22,28
+        ((64, 64, (1, 7), (1, 2)), 'tc'),   # amoebanet/operations.py:71-84
+        ((64, 64, (7, 1), (2, 1)), 'tc'),
+        ((64, 64, 3, 1), 'tc'),
+    ]
+    for (c_in, c_out, k, s), want in cases:
+        assert TF.conv_kind(c_in, c_out, k, s, 1, 1) == want, (c_in, c_out, k, s)
+    assert TF.conv_kind(64, 64, 3, 1, 2, 1) is None          # dilation
+    assert TF.conv_kind(64, 64, 3, 1, 1, 2) is None          # groups
+    assert TF.conv_kind(64, 64, 3, 4, 1, 1) is None          # stride 4x4
+    assert TF.conv_kind(6, 64, 3, 1, 1, 1) is None           # 6 input channels
+    assert TF.conv_kind(3, 64, (3, 9), 1, 1, 1) is None      # filter row longer than a K block
+
+
+def test_amoebanet_conversion_fuses_cells_and_keeps_keys_and_numbers_on_cpu():
+    import copy
+    import torch
+    from torchgpipe_b200 import ops
+    from torchgpipe_b200.models import amoebanetd
+    from torchgpipe_b200.ops.modules import AmoebaCell, AmoebaFactorizedReduce, AmoebaStem
+    torch.manual_seed(0)
+    # float64: with batch 2 and BatchNorm on 7x7 maps, fp32 summation order alone moves gradients
+    # by 1 % - in double the fused and the plain model agree to 1e-13
+    plain = amoebanetd(num_classes=10, num_layers=3, num_filters=64).double()
+    fused = ops.convert_to_sm100(copy.deepcopy(plain))
+    assert len(fused) == len(plain)
+    assert list(fused.state_dict().keys()) == list(plain.state_dict().keys())
+    assert isinstance(fused[0], AmoebaStem)
+    assert all(isinstance(layer, AmoebaCell) for layer in list(fused)[1:-1])
+    assert any(isinstance(m, AmoebaFactorizedReduce) for m in fused.modules())
+    # on CPU the fused modules take their ATen paths: shared ReLU and folded sums must not change
+    # the numbers (outputs, gradients, running statistics)
+    x = torch.randn(2, 3, 224, 224).double()
+    a, b = plain(x), fused(x)
+    assert torch.allclose(a, b, atol=1e-10)
+    a.square().mean().backward()
+    b.square().mean().backward()
+    for (n, p), (_, q) in zip(plain.named_parameters(), fused.named_parameters()):
+        assert torch.allclose(p.grad, q.grad, rtol=1e-8, atol=1e-12), n
+    for (n, p), (_, q) in zip(plain.named_buffers(), fused.named_buffers()):
+        assert torch.allclose(p.double(), q.double(), atol=1e-10), n
+    # converting twice is the identity
+    assert ops.convert_to_sm100(fused)[1] is fused[1]
+
+
+def test_graph_capture_key_separates_training_from_evaluation():
+    import torch
+    from torch import nn
+    from torchgpipe_b200.runtime.graphs import _signature
+    m = nn.Sequential(nn.Dropout(0.5))
+    x = (torch.zeros(2, 3),)
+    m.train()
+    with torch.enable_grad():
+        train_key = _signature(x, m)
+    m.eval()
+    with torch.no_grad():
+        eval_key = _signature(x, m)
+    with torch.enable_grad():
+        eval_grad_key = _signature(x, m)
+    assert len({train_key, eval_key, eval_grad_key}) == 3
+    assert _signature(x, m, grad=True) == eval_grad_key
+
+
+def test_link_bandwidth_comes_from_the_committed_measurement(monkeypatch):
+    from torchgpipe_b200.utils import link_bandwidth_gbs
+    monkeypatch.delenv('TGB_LINK_GBS', raising=False)
+    assert 600.0 < link_bandwidth_gbs() < 900.0          # profiles/p2p_bandwidth.json (775.2)
+    monkeypatch.setenv('TGB_LINK_GBS', '123.5')
+    assert link_bandwidth_gbs() == 123.5
