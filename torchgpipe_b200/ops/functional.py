@@ -648,6 +648,15 @@ def _bn_prepare(stats: Tensor, weight: Optional[Tensor], bias: Optional[Tensor],
     return coef, saved
 
 
+def _affine_grads(sums: Tensor, affine: Tuple[bool, bool]):
+    """(dgamma, dbeta) as contiguous rows of ONE transposed copy of the ``[C,2]`` sums table
+    (one small kernel instead of two strided clones per BatchNorm layer and micro-batch)."""
+    if not (affine[0] or affine[1]):
+        return None, None
+    rows = sums.t().contiguous()        # [2, C]: row 0 = sum dn = dbeta, row 1 = dgamma
+    return (rows[1] if affine[0] else None), (rows[0] if affine[1] else None)
+
+
 class _BatchNormAct(torch.autograd.Function):
     """z = act(BatchNorm(y)) in training mode from precomputed per-channel (sum, sum of squares).
 
@@ -691,8 +700,7 @@ class _BatchNormAct(torch.autograd.Function):
                                     _lib.ptr(sums), _lib.ptr(dy), _c_int(P), _c_int(C),
                                     _c_int(int(ctx.relu)), _lib.stream_ptr(y.device))
         _lib.check(rc, 'tgb_bn_act_bwd')
-        dweight = sums[:, 1].clone() if ctx.affine[0] else None
-        dbias = sums[:, 0].clone() if ctx.affine[1] else None
+        dweight, dbias = _affine_grads(sums, ctx.affine)
         return dy, None, dweight, dbias, None, None, None, None, None, None
 
 
@@ -967,8 +975,7 @@ class _BatchNormAddAct(torch.autograd.Function):
                                         _lib.ptr(dres), _c_int(P), _c_int(C),
                                         _c_int(int(ctx.relu)), _lib.stream_ptr(y.device))
         _lib.check(rc, 'tgb_bn_add_act_bwd')
-        dweight = sums[:, 1].clone() if ctx.affine[0] else None
-        dbias = sums[:, 0].clone() if ctx.affine[1] else None
+        dweight, dbias = _affine_grads(sums, ctx.affine)
         return dy, None, dweight, dbias, dres, None, None, None, None, None, None
 
 
