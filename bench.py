@@ -229,6 +229,33 @@ def timed_loop(torch, dist, step_fn, steps, warmup, devices, flush, world, reduc
     return ms, wall
 
 
+def resolve_balance(args, cfg, torch, dist, model, device, world, rank):
+    """The published balance (default, the headline), a comma list, or ``auto``: rank 0 times the
+    layers of the model it is about to run (``balance_by_time`` on its GPU, one micro-batch) and
+    every rank uses that split. A non-default balance is recorded in the JSON line
+    (``config.balance_source``); it is a second row next to the headline, never the headline."""
+    spec = args.balance
+    if spec in (None, '', 'reference'):
+        return list(cfg['balance']), 'reference'
+    n = len(cfg['balance'])
+    if spec != 'auto':
+        balance = [int(v) for v in spec.split(',')]
+        assert len(balance) == n and sum(balance) == sum(cfg['balance']), \
+            f'--balance needs {n} entries summing to {sum(cfg["balance"])}'
+        return balance, 'given'
+    box = [None]
+    if rank == 0:
+        from torchgpipe_b200.balance import balance_by_time
+        hw = MODEL_INFO[args.model]['hw']
+        sample = torch.rand(max(cfg['batch'] // cfg['chunks'], 1), 3, hw, hw)
+        box[0] = [int(v) for v in balance_by_time(n, model, sample, timeout=2.0, device=device,
+                                                 solver='optimal')]
+        torch.cuda.empty_cache()
+    if world > 1:
+        dist.broadcast_object_list(box, src=0)
+    return box[0], 'balance_by_time on the sm_100a operators (this run)'
+
+
 def metric_name(model):
     """Constant across N (the experiment name pipeline-N lives in config)."""
     return '%s GPipe training throughput' % MODEL_INFO[model]['metric']
@@ -421,7 +448,9 @@ def run_ours(args):
             plain = copy.deepcopy(model)
         model = ops.convert_to_sm100(model)
 
-    batch, chunks, balance = cfg['batch'], cfg['chunks'], cfg['balance']
+    batch, chunks = cfg['batch'], cfg['chunks']
+    balance, balance_source = resolve_balance(args, cfg, torch, dist, model, device, world, rank)
+    cfg = dict(cfg, balance=balance)
     host_input = torch.rand(batch, 3, hw, hw).pin_memory()
     loss_host = torch.zeros(1).pin_memory()
 
@@ -566,6 +595,7 @@ def run_ours(args):
         'config': {'model': MODEL_INFO[args.model]['name'],
                    'experiment': 'pipeline-%d' % n,
                    'global_batch': batch, 'chunks': chunks, 'balance': balance,
+                   'balance_source': balance_source,
                    'input': [3, MODEL_INFO[args.model]['hw'], MODEL_INFO[args.model]['hw']],
                    'checkpoint': 'except_last',
                    'optimizer': 'SGD(lr=0.1)', 'loss': MODEL_INFO[args.model]['loss'],
@@ -661,6 +691,12 @@ def run_reference(args):
         dist.init_process_group('nccl', device_id=device)
 
     batch, chunks, balance = cfg['batch'], cfg['chunks'], cfg['balance']
+    balance_source = 'reference'
+    if args.balance not in (None, '', 'reference'):
+        assert args.balance != 'auto', 'give the reference arm the list the other arm printed'
+        balance = [int(v) for v in args.balance.split(',')]
+        assert len(balance) == n and sum(balance) == sum(cfg['balance'])
+        balance_source = 'given'
     driver = rank == 0
     flush = L2Flusher(torch, device)
     host_input = torch.rand(batch, 3, hw, hw).pin_memory()
@@ -719,6 +755,7 @@ def run_reference(args):
         'config': {'model': MODEL_INFO[args.model]['name'],
                    'experiment': 'pipeline-%d' % n,
                    'global_batch': batch, 'chunks': chunks, 'balance': balance,
+                   'balance_source': balance_source,
                    'input': [3, MODEL_INFO[args.model]['hw'], MODEL_INFO[args.model]['hw']],
                    'checkpoint': 'except_last',
                    'optimizer': 'SGD(lr=0.1)', 'loss': MODEL_INFO[args.model]['loss'],
@@ -763,6 +800,9 @@ def main():
     p.add_argument('--no-secondary', action='store_true',
                    help='do not measure AmoebaNet-D(18,256) n{N}m32 after the U-Net headline')
     p.add_argument('--secondary-timeout', type=int, default=900)
+    p.add_argument('--balance', default='reference',
+                   help="'reference' (the published balance, default), 'auto' (ours arm: "
+                        "balance_by_time on the operators that run) or a comma list")
     p.add_argument('--child', action='store_true', help=argparse.SUPPRESS)
     args = p.parse_args()
     if args.gpus not in EXPERIMENTS[args.model]:
