@@ -98,6 +98,37 @@ def test_balance_by_time_cuda_events():
 
 
 @pytest.mark.gpu
+def test_time_profiler_measures_device_time_on_graph_replays():
+    """Layers much faster than their Python launch cost: eager event timing sees the host,
+    graph-replay timing sees the device. A 16x wider layer must look clearly more expensive in
+    graph mode; skip connections (stash / pop run twice per layer) must not break the capture."""
+    from torchgpipe_b200 import ops
+    from torchgpipe_b200.balance.profile import LayerLab, _fresh_leaves, _graphed_times
+    from torchgpipe_b200.models import unet
+    device = torch.device('cuda')
+    model = ops.convert_to_sm100(unet(depth=2, num_convs=2, base_channels=32))
+    lab = LayerLab(model, device)
+    seed = _fresh_leaves(torch.rand(4, 3, 64, 64), device)
+    times = _graphed_times(lab, seed, replays=3)
+    assert times is not None and len(times) == len(model)       # no silent fallback
+    assert all(len(t) == 3 and min(t) >= 0 for t in times)
+
+    small, big = nn.Conv2d(16, 16, 3, padding=1), nn.Conv2d(256, 256, 3, padding=1)
+    pair = nn.Sequential(small, nn.Conv2d(16, 256, 1), big)
+    us = balance_profile_times(pair, torch.rand(8, 16, 64, 64), device)
+    assert us[2] > 4 * us[0]
+    del lab, times, seed
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+
+
+def balance_profile_times(model, sample, device):
+    from torchgpipe_b200.balance.profile import profile_times
+    return profile_times(model, sample, 0.1, device)
+
+
+@pytest.mark.gpu
 def test_balance_by_size_latent():
     class Expand(nn.Module):
         def __init__(self, times):

@@ -10,13 +10,18 @@ gradients). How it is measured is different:
   multi-billion-parameter model that upload dominates what is being timed. Layers stay resident
   on the device while they fit a share of its free memory and are streamed one at a time beyond
   that;
-* on CUDA a pass records one event pair per layer on the stream and synchronises once at its
-  end, instead of a host clock between two device-wide synchronisations per layer;
+* on CUDA every layer's forward+backward is captured into a CUDA graph and timed on replays, so
+  the numbers are device time even where Python cannot launch kernels as fast as a B200 runs
+  them (``TGB_PROFILE_MODE=eager``, or a layer that cannot be captured, falls back to one event
+  pair per layer around eager calls with a single synchronisation per pass - the reference uses
+  a host clock between two device-wide synchronisations per layer);
 * the per-layer result is the median over the passes (times the number of passes, to keep the
   reference's "accumulated microseconds" scale), so a lazy-initialisation outlier in the first
   pass does not tilt the balance.
 """
 import copy
+import gc
+import os
 import statistics
 import time
 from typing import Iterator, List, Optional, Tuple, Union
@@ -128,6 +133,64 @@ def _one_pass_cuda(lab: LayerLab, seed: Batch) -> List[float]:
     return [b.elapsed_time(e) * 1e-3 for b, e in marks]
 
 
+def _graphed_times(lab: LayerLab, seed: Batch, replays: int) -> Optional[List[List[float]]]:
+    """Per-layer GPU time of forward+backward measured on CUDA-graph replays.
+
+    On a B200 most layers of the benchmark models finish faster than Python can launch their
+    kernels, so events around eager calls measure the host, not the device, and a balance built
+    from them is off. Each layer's forward+backward is therefore captured once into a CUDA graph
+    (static input = the static output of the previous layer's graph) and replayed ``replays``
+    times between two events: launch gaps disappear and what remains is device time.
+    Returns ``replays`` samples per layer, or ``None`` when some layer cannot be captured (it
+    synchronises with the host, for instance) - the caller then falls back to eager timing.
+    """
+    from torchgpipe_b200.skip.tracker import SkipTracker, use_skip_tracker
+
+    class _KeepingTracker(SkipTracker):
+        """Every layer runs twice here (eagerly, then under capture): a popped skip tensor
+        stays available for the second run."""
+
+        def load(self, batch, ns, name):        # type: ignore[override]
+            return self.tensors[(ns, name)]
+
+    device = lab.device
+    stream = torch.cuda.Stream(device)
+    graphs, marks = [], []
+    batch = seed
+    try:
+        with torch.cuda.device(device), use_skip_tracker(_KeepingTracker()):
+            stream.wait_stream(torch.cuda.current_stream(device))
+            for layer in lab:
+                batch = _fresh_leaves(batch.tensor_or_tensors)
+                with torch.cuda.stream(stream):            # lazy initialisation outside capture
+                    _forward_backward(layer, batch)
+                stream.synchronize()
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, stream=stream, capture_error_mode='relaxed'):
+                    out = _forward_backward(layer, batch)
+                samples = []
+                with torch.cuda.stream(stream):
+                    graph.replay()                          # outputs hold real values
+                    for _ in range(replays):
+                        begin = torch.cuda.Event(enable_timing=True)
+                        end = torch.cuda.Event(enable_timing=True)
+                        begin.record(stream)
+                        graph.replay()
+                        end.record(stream)
+                        samples.append((begin, end))
+                graphs.append(graph)                        # keeps the static tensors alive
+                marks.append(samples)
+                batch = out
+            stream.synchronize()
+            times = [[b.elapsed_time(e) * 1e-3 for b, e in samples] for samples in marks]
+    except Exception:
+        torch.cuda.synchronize(device)
+        return None
+    finally:
+        del graphs
+    return times
+
+
 def _one_pass_host(lab: LayerLab, seed: Batch) -> List[float]:
     seconds = []
     batch = seed
@@ -150,6 +213,14 @@ def profile_times(module: nn.Sequential, sample: TensorOrTensors, timeout: float
     seed = _fresh_leaves(sample, device)
     one_pass = _one_pass_cuda if device.type == 'cuda' else _one_pass_host
 
+    if device.type == 'cuda' and os.environ.get('TGB_PROFILE_MODE', 'graph') == 'graph' \
+            and lab.streamed == 0:
+        graphed = _graphed_times(lab, seed, replays=5)
+        lab.clear_gradients()
+        if graphed is not None:
+            return [max(1, int(statistics.median(bucket) * len(bucket) * 1_000_000))
+                    for bucket in graphed]
+
     samples: List[List[float]] = [[] for _ in range(len(lab))]
     deadline = time.monotonic() + timeout
     passes = 0
@@ -168,6 +239,14 @@ def profile_sizes(module: nn.Sequential, input: TensorOrTensors, chunks: int,
     if device.type != 'cuda':
         raise ValueError('size profiler supports only CUDA device')
 
+    # garbage from earlier work must not be freed in the middle of a measurement: the allocator
+    # counter would drop and a layer would seem to release memory
+    gc.collect()
+    # cuBLAS takes its per-stream workspace from the caching allocator on the first matmul of a
+    # stream; get that out of the way so it is not billed to the first layer that multiplies
+    warm = torch.zeros(8, 8, device=device)
+    torch.mm(warm, warm)
+    del warm
     whole = Batch(input)
     per_microbatch = whole[0].size(0) / chunks
     batch = _fresh_leaves(input, device, first_n=1)     # measure with one sample, then scale
@@ -179,7 +258,7 @@ def profile_sizes(module: nn.Sequential, input: TensorOrTensors, chunks: int,
         batch = _fresh_leaves(batch.tensor_or_tensors)
         held_before = torch.cuda.memory_allocated(device)
         batch = batch.call(layer)
-        grown = torch.cuda.memory_allocated(device) - held_before
+        grown = max(0, torch.cuda.memory_allocated(device) - held_before)
         weights = sum(p.numel() * p.element_size() for p in layer.parameters())
         sizes.append(int(grown * per_microbatch + weights * param_scale))
     return sizes
