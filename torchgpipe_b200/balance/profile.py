@@ -246,6 +246,7 @@ def profile_sizes(module: nn.Sequential, input: TensorOrTensors, chunks: int,
     # stream; get that out of the way so it is not billed to the first layer that multiplies
     warm = torch.zeros(8, 8, device=device)
     torch.mm(warm, warm)
+    torch.nn.functional.linear(warm, warm, warm[0])     # addmm: the cuBLASLt workspace
     del warm
     whole = Batch(input)
     per_microbatch = whole[0].size(0) / chunks
