@@ -116,3 +116,64 @@ def test_spawn_workers_joins_on_exception():
             raise RuntimeError('boom')
     time.sleep(0.05)
     assert threading.active_count() == before
+
+
+def test_graph_engine_mailboxes_wake_up_when_another_stage_fails():
+    """The in-process transport of GPipe(cuda_graphs=True): a stage blocked on a mailbox must
+    stop as soon as some other stage has failed (no GPU needed for this part)."""
+    import queue
+    import threading
+    import time
+    from torchgpipe_b200.runtime.graph_pipeline import PipelineAborted, _Mailboxes, _StageThread
+    boxes, lock, failed = {}, threading.Lock(), threading.Event()
+    a, b = _Mailboxes(0, boxes, lock, failed), _Mailboxes(1, boxes, lock, failed)
+    a.send(1, ('fwd', 0, 0), 'payload')
+    assert b.recv(0, ('fwd', 0, 0)) == 'payload'
+    # messages are keyed by (destination, source, key): nothing crosses over
+    a.send(1, ('fwd', 1, 0), 'x')
+    b.send(0, ('bwd', 1, 0), 'y')
+    assert a.recv(1, ('bwd', 1, 0)) == 'y' and b.recv(0, ('fwd', 1, 0)) == 'x'
+
+    got = []
+
+    def waiter():
+        try:
+            b.recv(0, ('fwd', 7, 0))
+        except PipelineAborted as exc:
+            got.append(str(exc))
+
+    t = threading.Thread(target=waiter)
+    t.start()
+    time.sleep(0.2)
+    failed.set()
+    t.join(timeout=5)
+    assert not t.is_alive() and got and 'another stage failed' in got[0]
+
+    # the stage thread delivers results and exceptions to the submitter and ends on None
+    import torch
+    worker = _StageThread.__new__(_StageThread)
+    threading.Thread.__init__(worker, daemon=True)
+    worker.device, worker.jobs = torch.device('cpu'), queue.Queue()
+    worker.run = lambda: _run_without_cuda(worker)     # no torch.cuda.set_device on this box
+    worker.start()
+    ok = worker.submit(lambda: 41 + 1)
+    bad = worker.submit(lambda: 1 / 0)
+    ok[0].wait(5), bad[0].wait(5)
+    assert ok[1] == (True, 42) and bad[1][0] is False and isinstance(bad[1][1], ZeroDivisionError)
+    worker.jobs.put(None)
+    worker.join(timeout=5)
+    assert not worker.is_alive()
+
+
+def _run_without_cuda(worker):
+    while True:
+        job = worker.jobs.get()
+        if job is None:
+            return
+        fn, box = job
+        try:
+            box.append((True, fn()))
+        except BaseException as exc:
+            box.append((False, exc))
+        finally:
+            box[0].set()

@@ -153,9 +153,17 @@ class GraphedPipeline:
         self._anchor = torch.zeros((), device=self.devices[-1], requires_grad=True)
 
     def close(self) -> None:
+        """Ends the stage threads (they are daemons, but a long-lived process that builds many
+        pipelines should not collect idle threads)."""
         for t in self._threads:
             t.jobs.put(None)
         self._threads = []
+
+    def __del__(self) -> None:
+        try:
+            self.close()
+        except Exception:       # interpreter shutdown: queues may already be gone
+            pass
 
     def native_launches_replayed(self) -> int:
         return sum(s.native_launches_replayed() for s in self.stages)
