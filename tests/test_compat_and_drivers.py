@@ -134,3 +134,43 @@ def test_bench_experiment_tables_match_the_reference_configs():
         for cfg in bench.EXPERIMENTS[model].values():
             assert sum(cfg['balance']) == sizes
             assert cfg['batch'] % cfg['chunks'] == 0 or model == 'resnet101'
+
+
+def test_bench_helpers_metric_balance_and_dropout_switch():
+    """Host-side pieces of bench.py that the driver's records depend on."""
+    import argparse
+    import torch
+    from torch import nn
+    sys.path.insert(0, ROOT)
+    import bench
+    # the metric string must not change with N (the driver checks consistency across the curve)
+    assert bench.metric_name('unet') == 'U-Net(5,64) GPipe training throughput'
+    assert 'pipeline' not in bench.metric_name('unet')
+
+    cfg = bench.EXPERIMENTS['unet'][4]
+    args = argparse.Namespace(balance='reference', model='unet')
+    assert bench.resolve_balance(args, cfg, torch, None, None, None, 1, 0) == \
+        ([30, 66, 84, 61], 'reference')
+    args.balance = '28,61,99,53'
+    assert bench.resolve_balance(args, cfg, torch, None, None, None, 1, 0) == \
+        ([28, 61, 99, 53], 'given')
+    args.balance = '1,2,3'
+    with pytest.raises(AssertionError):
+        bench.resolve_balance(args, cfg, torch, None, None, None, 1, 0)
+
+    # the numerics check turns every channel dropout off and restores it afterwards
+    from torchgpipe_b200.ops.modules import ConvInstNormLeaky
+    model = nn.Sequential(nn.Dropout2d(0.1),
+                          ConvInstNormLeaky(nn.Conv2d(4, 4, 3, padding=1, bias=False), 0.1, 1e-5,
+                                            0.01))
+    saved = bench.set_dropout(model, 0.0)
+    assert model[0].p == 0.0 and model[1].p == 0.0 and len(saved) == 2
+    bench.set_dropout(model, saved=saved)
+    assert model[0].p == 0.1 and model[1].p == 0.1
+
+    # AmoebaNet-D has no 1-GPU experiment in the reference: the secondary block says so
+    args = argparse.Namespace(gpus=1, no_secondary=False, child=False, model='unet')
+    note = bench.run_secondary(args, torch, None, 0, 0, 1, None)
+    assert 'skipped' in note and 'n2, n4, n8' in note['skipped']
+    args.child = True
+    assert bench.run_secondary(args, torch, None, 0, 0, 1, None) is None
