@@ -799,7 +799,8 @@ def main():
                    help='ours arm: skip the plain-PyTorch numerics comparison before timing')
     p.add_argument('--no-secondary', action='store_true',
                    help='do not measure AmoebaNet-D(18,256) n{N}m32 after the U-Net headline')
-    p.add_argument('--secondary-timeout', type=int, default=900)
+    p.add_argument('--secondary-timeout', type=int, default=400,
+                   help='seconds; keeps headline + secondary inside the per-N limit of the driver')
     p.add_argument('--balance', default='reference',
                    help="'reference' (the published balance, default), 'auto' (ours arm: "
                         "balance_by_time on the operators that run) or a comma list")
