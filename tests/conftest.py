@@ -24,23 +24,35 @@ def pytest_collection_modifyitems(config, items):
 
 
 @pytest.fixture(autouse=True)
-def manual_seed_zero():
+def _same_seed_for_every_test():
     torch.manual_seed(0)
+
+
+class _DeviceSleeper:
+    """``sleeper(seconds)`` enqueues a spin kernel of about that length on the current stream.
+
+    ``torch.cuda._sleep`` counts clock cycles, so the rate is calibrated once per session: the
+    median of three timed probes (the first one also absorbs context creation)."""
+
+    PROBE_CYCLES = 2_000_000
+
+    def __init__(self):
+        torch.cuda.init()
+        rates = []
+        for _ in range(3):
+            before = torch.cuda.Event(enable_timing=True)
+            after = torch.cuda.Event(enable_timing=True)
+            before.record()
+            torch.cuda._sleep(self.PROBE_CYCLES)
+            after.record()
+            after.synchronize()
+            rates.append(self.PROBE_CYCLES / before.elapsed_time(after))    # cycles per ms
+        self.cycles_per_second = 1e3 * sorted(rates)[1]
+
+    def __call__(self, seconds):
+        torch.cuda._sleep(int(seconds * self.cycles_per_second))
 
 
 @pytest.fixture(scope='session')
 def cuda_sleep():
-    """``cuda_sleep(seconds)`` enqueues a busy-wait kernel of roughly that length."""
-    torch.empty(1, device='cuda')
-    start = torch.cuda.Event(enable_timing=True)
-    end = torch.cuda.Event(enable_timing=True)
-    start.record()
-    torch.cuda._sleep(1000000)
-    end.record()
-    end.synchronize()
-    cycles_per_ms = 1000000 / start.elapsed_time(end)
-
-    def sleep(seconds):
-        torch.cuda._sleep(int(seconds * cycles_per_ms * 1000))
-
-    return sleep
+    return _DeviceSleeper()
