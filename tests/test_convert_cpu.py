@@ -223,3 +223,33 @@ def test_link_bandwidth_comes_from_the_committed_measurement(monkeypatch):
     assert 600.0 < link_bandwidth_gbs() < 900.0          # profiles/p2p_bandwidth.json (775.2)
     monkeypatch.setenv('TGB_LINK_GBS', '123.5')
     assert link_bandwidth_gbs() == 123.5
+
+
+def test_absorbed_batchnorm_deferred_statistics_on_cpu():
+    """The fused layer's BatchNorm under DeferredBatchNorm semantics (ATen path of the same
+    bookkeeping the sm_100a path uses): running estimates move once per mini-batch and equal the
+    full-batch ones."""
+    import copy
+    from torch import nn
+    from torchgpipe_b200 import ops
+    from torchgpipe_b200.batchnorm import DeferredBatchNorm, MiniBatchMoments
+    torch.manual_seed(23)
+    plain = nn.Sequential(nn.Conv2d(32, 64, 3, padding=1, bias=False), nn.BatchNorm2d(64))
+    fused = ops.convert_to_sm100(copy.deepcopy(plain))
+    fused = DeferredBatchNorm.convert_deferred_batch_norm(fused, chunks=2)
+    bn = [m for m in fused.modules() if isinstance(m, ops.modules.AbsorbedBatchNorm2d)][0]
+    assert bn.deferred_chunks == 2 and isinstance(bn.moments, MiniBatchMoments)
+    assert {'sum', 'sum_squares'} <= set(dict(bn.named_buffers()))
+    x = torch.randn(8, 32, 12, 12) * 3
+    plain(x)
+    first, second = x.chunk(2)
+    before = bn.running_mean.clone()
+    fused(first)
+    assert bn.tracked == 1 and bn.counter == 4 * 12 * 12 and torch.equal(bn.running_mean, before)
+    fused(second)
+    assert int(bn.num_batches_tracked) == 1 and bn.tracked == 0 and bn.counter == 0
+    assert torch.allclose(bn.running_mean, plain[1].running_mean, atol=1e-4)
+    assert torch.allclose(bn.running_var, plain[1].running_var, rtol=2e-2, atol=1e-3)
+    clone = copy.deepcopy(fused)
+    cbn = [m for m in clone.modules() if isinstance(m, ops.modules.AbsorbedBatchNorm2d)][0]
+    assert cbn.moments.owner is cbn

@@ -11,55 +11,68 @@ from torchgpipe_b200.checkpoint import checkpoint
 CHUNKS = 4
 
 
-def tilt_dist(input):
-    # make per-chunk statistics differ from the full batch's
-    rgb = input.transpose(0, 1)
-    rgb[0] *= 1
-    rgb[1] *= 10
-    rgb[2] *= 100
-    means = torch.tensor([[[[2.]]], [[[5.]]], [[[7.]]]])
-    input = input + means.transpose(0, 1) * torch.arange(input.size(0)).view(-1, 1, 1, 1)
-    return input
+def drifting_batch(samples=16, hw=32):
+    """Channels on very different scales whose mean also drifts from sample to sample, so the
+    statistics of a quarter of the batch are nowhere near those of the whole batch."""
+    scale = torch.tensor([1.0, 10.0, 100.0]).view(1, 3, 1, 1)
+    drift = torch.tensor([2.0, 5.0, 7.0]).view(1, 3, 1, 1)
+    position = torch.arange(samples, dtype=torch.float32).view(-1, 1, 1, 1)
+    return torch.rand(samples, 3, hw, hw) * scale + drift * position
 
 
-def chunked_forward(model, input, chunks=CHUNKS):
-    return torch.cat([model(c) for c in input.chunk(chunks)])
+def run_in_micro_batches(model, input, chunks=CHUNKS):
+    return torch.cat([model(piece) for piece in input.chunk(chunks)])
 
 
 @pytest.mark.parametrize('chunks', [1, 4])
 @pytest.mark.parametrize('input_requires_grad', [True, False])
 def test_output_and_grad_equal_batchnorm_per_chunk(chunks, input_requires_grad):
-    bn = nn.BatchNorm2d(3)
-    dbn = DeferredBatchNorm.convert_deferred_batch_norm(deepcopy(bn), chunks=chunks)
+    plain = nn.BatchNorm2d(3)
+    deferred = DeferredBatchNorm.convert_deferred_batch_norm(deepcopy(plain), chunks=chunks)
 
-    input = torch.rand(16, 3, 224, 224)
-    input = tilt_dist(input)
-    a = input.clone().requires_grad_(input_requires_grad)
-    b = input.clone().requires_grad_(input_requires_grad)
+    data = drifting_batch(hw=64)
+    x_plain = data.clone().requires_grad_(input_requires_grad)
+    x_deferred = data.clone().requires_grad_(input_requires_grad)
 
-    out1 = chunked_forward(bn, a, chunks)
-    out2 = chunked_forward(dbn, b, chunks)
-    assert torch.allclose(out1, out2, atol=1e-4)
+    y_plain = run_in_micro_batches(plain, x_plain, chunks)
+    y_deferred = run_in_micro_batches(deferred, x_deferred, chunks)
+    assert torch.allclose(y_plain, y_deferred, atol=1e-4)
 
-    out1.mean().backward()
-    out2.mean().backward()
-    assert torch.allclose(bn.weight.grad, dbn.weight.grad, atol=1e-4)
+    y_plain.mean().backward()
+    y_deferred.mean().backward()
+    assert torch.allclose(plain.weight.grad, deferred.weight.grad, atol=1e-4)
+    assert torch.allclose(plain.bias.grad, deferred.bias.grad, atol=1e-4)
     if input_requires_grad:
-        assert torch.allclose(a.grad, b.grad, atol=1e-4)
+        assert torch.allclose(x_plain.grad, x_deferred.grad, atol=1e-4)
 
 
 @pytest.mark.parametrize('momentum', [0.1, None])
 def test_running_stats_equal_full_batch(momentum):
-    bn = nn.BatchNorm2d(3, momentum=momentum)
-    dbn = DeferredBatchNorm.convert_deferred_batch_norm(deepcopy(bn), chunks=CHUNKS)
+    plain = nn.BatchNorm2d(3, momentum=momentum)
+    deferred = DeferredBatchNorm.convert_deferred_batch_norm(deepcopy(plain), chunks=CHUNKS)
 
-    input = tilt_dist(torch.rand(16, 3, 224, 224))
-    bn(input)
-    chunked_forward(dbn, input)
-    assert torch.allclose(bn.running_mean, dbn.running_mean, atol=1e-4)
-    assert torch.allclose(bn.running_var, dbn.running_var, atol=1e-4)
-    assert int(dbn.num_batches_tracked) == 1
-    assert dbn.sum.abs().sum() == 0 and dbn.counter == 0 and dbn.tracked == 0
+    for step in range(2):       # two mini-batches: the cumulative average has to advance too
+        data = drifting_batch(hw=64) + step
+        plain(data)
+        run_in_micro_batches(deferred, data)
+        assert torch.allclose(plain.running_mean, deferred.running_mean, rtol=1e-4, atol=1e-4)
+        # nn.BatchNorm commits the unbiased variance, the deferred layer the biased one
+        n = data.numel() // 3
+        assert torch.allclose(plain.running_var, deferred.running_var, rtol=2.0 / n + 1e-4, atol=1e-3)
+        assert int(deferred.num_batches_tracked) == step + 1
+        assert deferred.sum.abs().sum() == 0 and deferred.counter == 0 and deferred.tracked == 0
+
+
+def test_partial_mini_batch_leaves_running_stats_alone():
+    deferred = DeferredBatchNorm(3, chunks=CHUNKS)
+    before = deferred.running_mean.clone()
+    pieces = drifting_batch().chunk(CHUNKS)
+    for k, piece in enumerate(pieces[:-1]):
+        deferred(piece)
+        assert deferred.tracked == k + 1 and deferred.counter == (k + 1) * piece.numel() // 3
+        assert torch.equal(deferred.running_mean, before)
+    deferred(pieces[-1])
+    assert not torch.equal(deferred.running_mean, before) and deferred.tracked == 0
 
 
 def test_convert_rules():
@@ -93,9 +106,9 @@ def test_state_dict_has_accumulators():
 def test_eval_uses_running_stats():
     bn = nn.BatchNorm2d(3)
     dbn = DeferredBatchNorm.convert_deferred_batch_norm(deepcopy(bn), chunks=CHUNKS)
-    input = tilt_dist(torch.rand(16, 3, 32, 32))
+    input = drifting_batch()
     bn(input)
-    chunked_forward(dbn, input)
+    run_in_micro_batches(dbn, input)
     bn.eval()
     dbn.eval()
     assert torch.allclose(bn(input), dbn(input), atol=1e-1, rtol=1e-3)
@@ -107,9 +120,9 @@ def test_optimize_like_batchnorm():
     dbn = DeferredBatchNorm.convert_deferred_batch_norm(deepcopy(bn), chunks=CHUNKS)
     opt = optim.SGD(chain(bn.parameters(), dbn.parameters()), lr=1.0)
     for i in range(5):
-        input = tilt_dist(torch.rand(16, 3, 32, 32))
+        input = drifting_batch()
         a = bn(input).sum()
-        b = chunked_forward(dbn, input).sum()
+        b = run_in_micro_batches(dbn, input).sum()
         (a + b).backward()
         opt.step()
         opt.zero_grad()
@@ -120,11 +133,11 @@ def test_optimize_like_batchnorm():
 def test_conv_then_bn():
     bn = nn.Sequential(nn.Conv2d(3, 3, 1), nn.BatchNorm2d(3))
     dbn = DeferredBatchNorm.convert_deferred_batch_norm(deepcopy(bn), chunks=CHUNKS)
-    input = tilt_dist(torch.rand(16, 3, 32, 32))
+    input = drifting_batch()
     opt = optim.SGD(chain(bn.parameters(), dbn.parameters()), lr=0.1)
     a = bn(input)
     a.sum().backward()
-    b = chunked_forward(dbn, input)
+    b = run_in_micro_batches(dbn, input)
     b.sum().backward()
     opt.step()
     assert torch.allclose(bn[0].weight, dbn[0].weight, atol=1e-3)

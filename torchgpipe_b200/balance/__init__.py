@@ -42,74 +42,50 @@ def balance_cost(cost: List[int], partitions: int, solver: str = 'reference') ->
     return [len(block) for block in solve(cost, partitions)]
 
 
-def balance_by_time(partitions: int,
-                    module: nn.Sequential,
-                    sample: TensorOrTensors,
-                    *,
-                    timeout: float = 1.0,
-                    device: Device = torch.device('cuda'),
-                    solver: str = 'reference',
-                    ) -> List[int]:
-    """Balances by measured forward+backward time of each layer.
+def balance_by_time(partitions: int, module: nn.Sequential, sample: TensorOrTensors, *,
+                    timeout: float = 1.0, device: Device = torch.device('cuda'),
+                    solver: str = 'reference') -> List[int]:
+    """Layer counts per stage such that the stages take about equally long.
 
-    Args:
-        partitions: number of stages wanted.
-        module: sequential module to balance.
-        sample: example input (any batch size), on the same device as ``module``.
+    Every layer's forward+backward is measured in isolation on ``device`` with ``sample`` as the
+    model input (any batch size; use one *micro*-batch to balance for the shapes the pipeline
+    will actually run). On a CUDA device the measurement is device time taken on CUDA-graph
+    replays of each layer - see :mod:`torchgpipe_b200.balance.profile` for why event pairs around
+    eager calls are not good enough on a B200 - and ``timeout`` only bounds the eager fallback,
+    which repeats its passes until that many seconds are over. On CPU the host clock is used.
 
-    Keyword Args:
-        timeout: keep re-profiling until this many seconds have passed (default 1.0).
-        device: CPU or CUDA device to profile on (default: current CUDA device).
-            On CUDA, layers are timed with CUDA events on the device, not with
-            the host clock.
-        solver: ``'reference'`` (default, the reference's heuristic) or ``'optimal'``
-            (exact min-max contiguous split; never yields an empty stage).
-
-    Returns:
-        list of layer counts, one per stage, for ``GPipe(balance=...)``.
+    ``solver='reference'`` splits the measured costs with the reference's heuristic;
+    ``solver='optimal'`` with an exact min-max contiguous split that never leaves a stage empty.
+    The result goes straight into ``GPipe(module, balance=...)``. ``module`` itself is not
+    moved, run or modified.
     """
     times = profile_times(module, sample, timeout, torch.device(device))
     return balance_cost(times, partitions, solver)
 
 
-def balance_by_size(partitions: int,
-                    module: nn.Sequential,
-                    input: TensorOrTensors,
-                    *,
-                    chunks: int = 1,
-                    param_scale: float = 2.0,
+def balance_by_size(partitions: int, module: nn.Sequential, input: TensorOrTensors, *,
+                    chunks: int = 1, param_scale: float = 2.0,
                     device: Device = torch.device('cuda'),
-                    solver: str = 'reference',
-                    ) -> List[int]:
-    """Balances by CUDA memory each layer needs for training.
+                    solver: str = 'reference') -> List[int]:
+    """Layer counts per stage such that the stages need about equally much device memory.
 
-    Per layer: ``activation bytes per sample x (batch / chunks) + parameter
-    bytes x param_scale``. ``param_scale`` accounts for what the optimiser keeps
-    per parameter besides the gradient:
+    The estimate for a layer is::
 
-    =========  =============  =========================================
-    Optimizer  `param_scale`  Internal state
-    =========  =============  =========================================
-    SGD        2--3           (momentum_buffer)
-    Adam       4--5           exp_avg, exp_avg_sq, (max_exp_avg_sq)
-    Adadelta   4              square_avg, acc_delta
-    Adagrad    3              sum
-    RMSprop    3--5           square_avg, (momentum_buffer), (grad_avg)
-    =========  =============  =========================================
+        bytes its forward leaves allocated for ONE sample x (len(input) / chunks)
+        + bytes of its parameters x param_scale
 
-    Args:
-        partitions: number of stages wanted.
-        module: sequential module to balance.
-        input: example mini-batch of the size used in training.
+    ``input`` is a mini-batch of the training size and ``chunks`` the number of micro-batches, so
+    the first term is what one micro-batch keeps alive. ``param_scale`` says how many
+    parameter-sized tensors training holds per parameter: the parameter, its gradient, and
+    whatever the optimiser keeps -
 
-    Keyword Args:
-        chunks: number of micro-batches used in training (default 1).
-        param_scale: copies of the parameters held during training (default 2.0).
-        device: CUDA device to profile on (CUDA only).
-        solver: as in :func:`balance_by_time`.
+    * plain SGD: 2 (parameter + gradient), 3 with momentum;
+    * Adagrad: 3 (its running sum); RMSprop: 3, up to 5 with momentum and centred variance;
+    * Adadelta: 4 (two running averages);
+    * Adam / AdamW: 4 (two moments), 5 with ``amsgrad``.
 
-    Returns:
-        list of layer counts, one per stage.
+    CUDA devices only (the numbers come from the caching allocator's counters). ``solver`` as in
+    :func:`balance_by_time`.
     """
     sizes = profile_sizes(module, input, chunks, param_scale, torch.device(device))
     return balance_cost(sizes, partitions, solver)

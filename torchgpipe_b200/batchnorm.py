@@ -16,7 +16,7 @@ biased ``E[x^2] - E[x]^2`` (reference ``:70-71``).
 On a B200 the per-channel sum / sum-of-squares come from one fused pass
 (``ops.channel_moments``) instead of two full-tensor reductions.
 """
-from typing import Optional, TypeVar, cast
+from typing import Optional, Tuple, TypeVar, cast
 
 import torch
 from torch import Tensor, nn
@@ -25,12 +25,12 @@ from torch.nn.modules.batchnorm import _BatchNorm
 
 from torchgpipe_b200.checkpoint import is_recomputing
 
-__all__ = ['DeferredBatchNorm']
+__all__ = ['DeferredBatchNorm', 'MiniBatchMoments']
 
 TModule = TypeVar('TModule', bound=nn.Module)
 
 
-def _channel_moments(input: Tensor):
+def _channel_moments(input: Tensor) -> Tuple[Tensor, Tensor]:
     """Per-channel (sum, sum of squares) over every dim but 1."""
     if input.is_cuda and input.dim() == 4:
         try:
@@ -43,77 +43,88 @@ def _channel_moments(input: Tensor):
     return input.sum(dims), (input * input).sum(dims)
 
 
+class MiniBatchMoments:
+    """The bookkeeping of one deferred BatchNorm: how many micro-batches and elements have been
+    folded into the owner's ``sum`` / ``sum_squares`` buffers, and the commit into its running
+    estimates once the mini-batch is complete.
+
+    Shared by :class:`DeferredBatchNorm` (torch arithmetic) and the fused layers' BatchNorm
+    (``ops.modules.AbsorbedBatchNorm2d``, whose moments come out of the convolution epilogue).
+    The tensors stay buffers of the owner so that ``state_dict`` has the reference's keys; only
+    the two host-side counts live here.
+    """
+
+    __slots__ = ('owner', 'chunks', 'elements', 'seen')
+
+    def __init__(self, owner: _BatchNorm, chunks: int) -> None:
+        self.owner = owner
+        self.chunks = chunks
+        self.elements = 0       # per channel, over the micro-batches seen so far
+        self.seen = 0           # micro-batches of the current mini-batch
+
+    def absorb(self, total: Tensor, total_of_squares: Tensor, elements: int) -> None:
+        """One micro-batch's per-channel moments; commits when it was the mini-batch's last."""
+        bn = self.owner
+        with torch.no_grad():
+            bn.sum += total
+            bn.sum_squares += total_of_squares
+            self.elements += elements
+            self.seen += 1
+            if self.seen == self.chunks:
+                self._commit()
+
+    def _commit(self) -> None:
+        bn = self.owner
+        bn.num_batches_tracked += 1
+        # momentum None: cumulative average over the mini-batches seen since reset
+        weight = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+        mean = bn.sum / self.elements
+        biased_var = bn.sum_squares / self.elements - mean * mean   # as nn.BatchNorm normalises
+        bn.running_mean.lerp_(mean, weight)
+        bn.running_var.lerp_(biased_var, weight)
+        bn.sum.zero_()
+        bn.sum_squares.zero_()
+        self.elements = self.seen = 0
+
+
 class DeferredBatchNorm(_BatchNorm):
     """BatchNorm that commits running statistics once per ``chunks`` micro-batches."""
 
     sum: Tensor
     sum_squares: Tensor
 
-    def __init__(self,
-                 num_features: int,
-                 eps: float = 1e-5,
-                 momentum: Optional[float] = 0.1,
-                 affine: bool = True,
-                 chunks: int = 1,
-                 ) -> None:
+    def __init__(self, num_features: int, eps: float = 1e-5, momentum: Optional[float] = 0.1,
+                 affine: bool = True, chunks: int = 1) -> None:
         super().__init__(num_features, eps, momentum, affine, track_running_stats=True)
-
         self.register_buffer('sum', torch.zeros_like(self.running_mean))
         self.register_buffer('sum_squares', torch.zeros_like(self.running_var))
-
-        self.counter = 0     # elements per channel accumulated so far
-        self.tracked = 0     # micro-batches accumulated so far
         self.chunks = chunks
+        self.moments = MiniBatchMoments(self, chunks)
+
+    # the reference's attribute names for the two counts
+    @property
+    def counter(self) -> int:
+        return self.moments.elements
+
+    @property
+    def tracked(self) -> int:
+        return self.moments.seen
 
     def _check_input_dim(self, input: Tensor) -> None:
         # Any (N, C, *) input is fine: 1-d, 2-d and 3-d BatchNorm alike.
         if input.dim() <= 2:
             raise ValueError('expected at least 3D input (got %dD input)' % input.dim())
 
-    def _track(self, input: Tensor) -> bool:
-        """Adds one micro-batch to the accumulators; True when the mini-batch is complete."""
-        with torch.no_grad():
-            s, ss = _channel_moments(input)
-            self.sum += s
-            self.sum_squares += ss
-
-        self.counter += input.numel() // input.size(1)
-        self.tracked += 1
-        return self.tracked == self.chunks
-
-    def _commit(self) -> None:
-        """Folds the accumulated mini-batch statistics into the running estimates."""
-        self.num_batches_tracked += 1
-        if self.momentum is None:
-            factor = 1.0 / float(self.num_batches_tracked)   # cumulative average
-        else:
-            factor = self.momentum                           # exponential average
-
-        mean = self.sum / self.counter
-        var = self.sum_squares / self.counter - mean ** 2
-
-        self.running_mean.mul_(1 - factor).add_(mean * factor)
-        self.running_var.mul_(1 - factor).add_(var * factor)
-
-        self.sum.zero_()
-        self.sum_squares.zero_()
-        self.counter = 0
-        self.tracked = 0
-
     def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
         self._check_input_dim(input)
-        if not self.training:
-            return F.batch_norm(input, self.running_mean, self.running_var,
-                                self.weight, self.bias,
-                                training=False, momentum=0.0, eps=self.eps)
-
-        if not is_recomputing():
-            if self._track(input):
-                self._commit()
-
-        # Normalise with this micro-batch's own statistics.
-        return F.batch_norm(input, None, None, self.weight, self.bias,
-                            training=True, momentum=0.0, eps=self.eps)
+        running = not self.training
+        if self.training and not is_recomputing():
+            # a recomputation sees the same micro-batch a second time: it must not count twice
+            self.moments.absorb(*_channel_moments(input), input.numel() // input.size(1))
+        # training: this micro-batch's own statistics, exactly like nn.BatchNorm would
+        return F.batch_norm(input, self.running_mean if running else None,
+                            self.running_var if running else None, self.weight, self.bias,
+                            training=not running, momentum=0.0, eps=self.eps)
 
     @classmethod
     def convert_deferred_batch_norm(cls, module: TModule, chunks: int = 1) -> TModule:

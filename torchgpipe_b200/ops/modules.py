@@ -6,6 +6,7 @@ from torch import Tensor, nn
 import torch.nn.functional as F
 
 from torchgpipe_b200.checkpoint import is_recomputing
+from torchgpipe_b200.batchnorm import MiniBatchMoments
 from torchgpipe_b200.ops import functional as TF
 
 __all__ = ['Absorbed', 'ConvInstNormLeaky', 'Conv2dTC', 'ConvBatchNormAct', 'AbsorbedBatchNorm2d',
@@ -156,8 +157,17 @@ class AbsorbedBatchNorm2d(nn.BatchNorm2d):
     """
 
     deferred_chunks = 0
-    counter = 0
-    tracked = 0
+    moments: Optional[MiniBatchMoments] = None
+
+    @property
+    def tracked(self) -> int:
+        """Micro-batches of the current mini-batch accumulated so far (DeferredBatchNorm's name)."""
+        return self.moments.seen if self.moments is not None else 0
+
+    @property
+    def counter(self) -> int:
+        """Elements per channel accumulated so far."""
+        return self.moments.elements if self.moments is not None else 0
 
     def forward(self, input: Tensor) -> Tensor:  # type: ignore[override]
         return input
@@ -173,26 +183,13 @@ class AbsorbedBatchNorm2d(nn.BatchNorm2d):
             self.register_buffer('sum', torch.zeros_like(self.running_mean))
             self.register_buffer('sum_squares', torch.zeros_like(self.running_var))
         self.deferred_chunks = chunks
-        self.counter = self.tracked = 0
+        self.moments = MiniBatchMoments(self, chunks)
 
     def track(self, stats: Tensor, count: int) -> None:
-        """Adds one micro-batch's (sum, sum of squares); commits after ``deferred_chunks``."""
-        with torch.no_grad():
-            self.sum += stats[:, 0]
-            self.sum_squares += stats[:, 1]
-            self.counter += count
-            self.tracked += 1
-            if self.tracked == self.deferred_chunks:
-                self.num_batches_tracked += 1
-                factor = (1.0 / float(self.num_batches_tracked) if self.momentum is None
-                          else self.momentum)
-                mean = self.sum / self.counter
-                var = self.sum_squares / self.counter - mean ** 2      # biased, as the reference
-                self.running_mean.mul_(1 - factor).add_(mean * factor)
-                self.running_var.mul_(1 - factor).add_(var * factor)
-                self.sum.zero_()
-                self.sum_squares.zero_()
-                self.counter = self.tracked = 0
+        """Adds one micro-batch's (sum, sum of squares) as produced by the convolution epilogue
+        (``stats[:, 0]``, ``stats[:, 1]``); the running estimates move once per mini-batch."""
+        assert self.moments is not None
+        self.moments.absorb(stats[:, 0], stats[:, 1], count)
 
 
 def _bn_running_args(bn: AbsorbedBatchNorm2d, stats: Tensor, count: int):

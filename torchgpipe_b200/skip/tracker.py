@@ -45,48 +45,52 @@ class SkipTracker:
 
 
 class SkipTrackerThroughPotals(SkipTracker):
-    """Tracker of one micro-batch inside a pipeline; cross-stage skips use portals."""
+    """Tracker of one micro-batch inside a pipeline.
+
+    A skip whose stash and pop sit on the same stage stays in the dictionary. One that crosses
+    stages gets a :class:`Portal`, and every operation on it threads a phony edge through the
+    first tensor of the batch so that autograd orders the portal's nodes with the stage's own
+    computation (``fork`` takes the edge out of the batch, ``join`` puts one back in).
+    """
 
     def __init__(self, skip_layout: SkipLayout) -> None:
         super().__init__()
         self.skip_layout = skip_layout
         self.portals: Dict[SkipKey, Portal] = {}
 
+    def _crosses_stages(self, ns: Namespace, name: str) -> bool:
+        return self.skip_layout.requires_copy(ns, name)
+
     def save(self, batch: Batch, ns: Namespace, name: str, tensor: Optional[Tensor]) -> None:
-        if not self.skip_layout.requires_copy(ns, name):
+        if not self._crosses_stages(ns, name):
             super().save(batch, ns, name, tensor)
             return
-
         key = (ns, name)
-        portal = self.portals.get(key)
-        if portal is None:
-            # First forward. Lives: blue() + orange(); one more orange() if the
-            # pop stage will be recomputed.
-            life = 3 if is_checkpointing() else 2
-            portal = Portal(tensor, life)
-            self.portals[key] = portal
-        else:
-            # Recomputation of the stash stage: only blue() takes it again.
+        if key in self.portals:
+            # the stashing stage is being recomputed: the portal exists, only its blue node
+            # will look at the tensor again
+            portal = self.portals[key]
             portal.put_tensor(tensor, 1)
-
-        phony = portal.blue()
-        batch[0] = join(batch[0], phony)
+        else:
+            # first forward: blue and orange each use the tensor once, and orange a second
+            # time if the popping stage is going to be recomputed
+            uses = 2 + int(is_checkpointing())
+            portal = self.portals[key] = Portal(tensor, uses)
+        batch[0] = join(batch[0], portal.blue())
 
     def load(self, batch: Batch, ns: Namespace, name: str) -> Optional[Tensor]:
-        if not self.skip_layout.requires_copy(ns, name):
+        if not self._crosses_stages(ns, name):
             return super().load(batch, ns, name)
-
-        portal = self.portals[(ns, name)]
-        batch[0], phony = fork(batch[0])
-        return portal.orange(phony)
+        batch[0], edge = fork(batch[0])
+        return self.portals[(ns, name)].orange(edge)
 
     def copy(self, batch: Batch, prev_stream: AbstractStream, next_stream: AbstractStream,
              ns: Namespace, name: str) -> None:
-        assert self.skip_layout.requires_copy(ns, name)
-        batch[0], phony = fork(batch[0])
-        portal = self.portals[(ns, name)]
-        phony = portal.copy(prev_stream, next_stream, phony)
-        batch[0] = join(batch[0], phony)
+        """Moves the portal's tensor to the popping stage's device, on the copy streams."""
+        assert self._crosses_stages(ns, name)
+        batch[0], edge = fork(batch[0])
+        arrived = self.portals[(ns, name)].copy(prev_stream, next_stream, edge)
+        batch[0] = join(batch[0], arrived)
 
 
 class _Current(threading.local):
